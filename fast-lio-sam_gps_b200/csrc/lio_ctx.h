@@ -1,0 +1,130 @@
+// Host-side context of the C-ABI in include/lio_b200.h: owns the stream, the map storage, the scan
+// buffers and the pinned result block.  Internal header (not part of the boundary).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/lio_b200.h"
+#include "lio_device.cuh"
+
+namespace lio {
+
+void set_error(const char* fmt, ...);
+bool cuda_ok(cudaError_t e, const char* what);
+
+#define LIO_CUDA(call)                                  \
+  do {                                                  \
+    if (!::lio::cuda_ok((call), #call)) return LIO_E_CUDA; \
+  } while (0)
+
+// result block written by the reduction kernel straight into mapped pinned host memory
+struct HShareOut {
+  double HTH[144];
+  double HTz[12];
+  double res_sum;
+  double n_eff;
+  unsigned long long seq;  // bumped by the kernel last, so the host can tell the block is complete
+  unsigned long long pad;
+};
+
+enum TimerId { T_KNN = 0, T_PLANE, T_INSERT, T_CLASSIFY, T_COUNT };
+
+struct EventPair {
+  cudaEvent_t a, b;
+  int id;
+};
+
+}  // namespace lio
+
+struct lio_ctx {
+  lio_config cfg;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int n_sms = 0;
+
+  // map
+  lio::MapView map{};
+  uint32_t table_cap = 0;
+  // scratch for insert batches
+  float4* batch_pts = nullptr;      // staged batch (device)
+  uint32_t* batch_ent = nullptr;    // hash slot of each batch point's cell
+  uint32_t* batch_tslot = nullptr;  // slot in the per-batch voxel table
+  unsigned long long* batch_ebest = nullptr;  // best existing (d,id) of the point's voxel
+  uint32_t* batch_ecnt = nullptr;             // existing points in the voxel
+  uint32_t batch_cap = 0;
+  unsigned long long* vox_keys = nullptr;  // per-batch voxel arbitration table
+  unsigned long long* vox_best = nullptr;
+  uint32_t vox_cap = 0;
+  float* boxes_dev = nullptr;  // up to 64 boxes
+
+  // scan
+  int scan_n = 0;
+  bool nn_valid = false;
+  float4* body = nullptr;   // max_scan
+  float4* world = nullptr;  // max_scan (w = unused)
+  float4* nn = nullptr;     // max_scan * 5 (xyz, id bits)
+  float* nn_d2 = nullptr;   // max_scan * 5
+  int* nn_cnt = nullptr;    // max_scan
+  uint8_t* sel = nullptr;   // max_scan
+  float4* plane = nullptr;  // max_scan: a b c pd2
+  double* rows = nullptr;   // max_scan * 13, allocated on first lio_h_share_rows
+  uint8_t* cls = nullptr;   // map_incremental class per point
+  uint32_t* blk_cnt = nullptr;  // per-block counts for the ordered compaction (2 x blocks)
+  float4* list_add = nullptr;
+  float4* list_nodown = nullptr;
+  double* state_dev = nullptr;  // 36 doubles
+  double* partials = nullptr;   // reduction partials
+  int partial_blocks = 0;
+
+  lio::HShareOut* out_host = nullptr;  // pinned + mapped
+  lio::HShareOut* out_dev = nullptr;   // device alias of out_host
+  unsigned long long out_seq = 0;
+
+  // pinned staging for uploads
+  float* stage_host = nullptr;
+  size_t stage_bytes = 0;
+
+  // fov_segment state
+  bool lm_init = false;
+  float lm_min[3]{}, lm_max[3]{};
+
+  // timing
+  bool timing = false;
+  std::vector<lio::EventPair> ev_used;
+  std::vector<lio::EventPair> ev_free;
+  double t_sum[lio::T_COUNT]{};
+  int t_n[lio::T_COUNT]{};
+  int64_t launches = 0;
+};
+
+namespace lio {
+
+// map (lio_map.cu)
+int map_alloc(lio_ctx* c);
+void map_free(lio_ctx* c);
+int map_clear(lio_ctx* c);
+int map_ensure_batch(lio_ctx* c, uint32_t n);
+int map_add_device(lio_ctx* c, const float4* pts, uint32_t n_max, const uint32_t* n_dev, bool downsample);
+int map_delete_boxes(lio_ctx* c, const float* boxes_host, int nb);
+int map_read_counters(lio_ctx* c, MapCounters* out);
+int map_export(lio_ctx* c, std::vector<float4>& out);
+
+// scan / measurement (lio_scan.cu)
+int scan_alloc(lio_ctx* c);
+void scan_free(lio_ctx* c);
+int scan_knn(lio_ctx* c, const double* state_host);
+int scan_plane_reduce(lio_ctx* c, const double* state_host, bool want_rows);
+int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inited);
+int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float4* out_nn, float* out_d2, int* out_cnt);
+
+// timing helpers (lio_capi.cu)
+void timer_begin(lio_ctx* c, int id);
+void timer_end(lio_ctx* c);
+
+// host esekf (esekf_host.cpp)
+int iekf_update_host(lio_ctx* c, double* state, double* P, double R, int max_iter, const double* limit, double* iter_states,
+                     int* n_eff_trace, int* knn_trace, int* iters_done);
+
+}  // namespace lio

@@ -1,0 +1,216 @@
+// Exact k<=5 nearest-neighbour search on the voxel-hashed map — kernel K3 of SURVEY.md §2.2.
+// Replaces KD_TREE::Nearest_Search (ikd-Tree, absent submodule): same result set,
+// canonical order ascending (squared distance, id).
+//
+// A group of G lanes (G = 8: one bucket = one 128-byte line per load) serves one query:
+//   ring 1 : the 27 cells around the query are probed by the lanes in parallel (all first-probe loads
+//            are issued before any is consumed), then every hit bucket is read with one coalesced
+//            float4-per-lane load; each lane keeps a sorted private top-5 of the slots it saw;
+//   merge  : 5 rounds of a butterfly min over the lanes' list heads yield the group's top-5 in lanes 0..4;
+//   rings 2..R are visited only while the 5th distance (or max_d2 when fewer than 5 were found) still
+//            exceeds the distance from the query to the boundary of the block already searched, with
+//            cells pruned by their box distance.  This is what makes the search exact.
+#pragma once
+#include "lio_device.cuh"
+
+namespace lio {
+
+struct TopList {  // ascending (d2 bits, id) keys with the slot they came from
+  unsigned long long k0, k1, k2, k3, k4;
+  uint32_t r0, r1, r2, r3, r4;
+  __device__ __forceinline__ void clear() {
+    k0 = k1 = k2 = k3 = k4 = ~0ull;
+    r0 = r1 = r2 = r3 = r4 = kNone;
+  }
+  __device__ __forceinline__ void insert(unsigned long long k, uint32_t r) {
+    if (k >= k4) return;
+    const bool c0 = k < k0, c1 = k < k1, c2 = k < k2, c3 = k < k3;
+    k4 = c3 ? k3 : k;  r4 = c3 ? r3 : r;
+    k3 = c2 ? k2 : (c3 ? k : k3);  r3 = c2 ? r2 : (c3 ? r : r3);
+    k2 = c1 ? k1 : (c2 ? k : k2);  r2 = c1 ? r1 : (c2 ? r : r2);
+    k1 = c0 ? k0 : (c1 ? k : k1);  r1 = c0 ? r0 : (c1 ? r : r1);
+    k0 = c0 ? k : k0;              r0 = c0 ? r : r0;
+  }
+  __device__ __forceinline__ void pop() {
+    k0 = k1; k1 = k2; k2 = k3; k3 = k4; k4 = ~0ull;
+    r0 = r1; r1 = r2; r2 = r3; r3 = r4; r4 = kNone;
+  }
+};
+
+template <int G>
+struct Group {
+  static_assert(G == 8 || G == 16 || G == 32, "lanes per query");
+  static constexpr int kSub = G / kSlots;  // buckets read per load instruction
+  unsigned mask;                           // lanes of this group within the warp
+  int gl;                                  // lane within the group
+  int base;                                // first warp lane of the group
+  __device__ __forceinline__ Group() {
+    const int lane = threadIdx.x & 31;
+    gl = lane & (G - 1);
+    base = lane - gl;
+    mask = (G == 32) ? 0xFFFFFFFFu : (((1u << G) - 1u) << base);
+  }
+  __device__ __forceinline__ unsigned ballot(bool p) const { return (__ballot_sync(mask, p) >> base) & ((G == 32) ? 0xFFFFFFFFu : ((1u << G) - 1u)); }
+  template <typename T>
+  __device__ __forceinline__ T shfl(T v, int src) const { return __shfl_sync(mask, v, base + src); }
+};
+
+// distance^2 from q to the axis-aligned box of cell (cx,cy,cz)
+__device__ __forceinline__ float cell_box_d2(float qx, float qy, float qz, int cx, int cy, int cz, float h) {
+  const float lx = (float)cx * h, ly = (float)cy * h, lz = (float)cz * h;
+  float dx = 0.f, dy = 0.f, dz = 0.f;
+  if (qx < lx) dx = lx - qx; else if (qx > lx + h) dx = qx - (lx + h);
+  if (qy < ly) dy = ly - qy; else if (qy > ly + h) dy = qy - (ly + h);
+  if (qz < lz) dz = lz - qz; else if (qz > lz + h) dz = qz - (lz + h);
+  return dx * dx + dy * dy + dz * dz;
+}
+
+// read the chain of one cell; every lane of the group looks at slot (gl % 8) of bucket sub = gl / 8
+template <int G>
+__device__ __forceinline__ void scan_chain(const MapView& m, const Group<G>& g, uint32_t head, uint32_t ovf, float qx, float qy,
+                                           float qz, uint32_t max_bits, TopList& L) {
+  // kSub > 1: callers hand different chains to different sub-groups, so this routine only walks one chain
+  uint32_t b = head;
+  while (b != kNone) {
+    const uint32_t ref = b * kSlots + (g.gl & (kSlots - 1));
+    const float4 p = __ldg(m.slots + ref);
+    const uint32_t id = __float_as_uint(p.w);
+    const float d2 = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+    const uint32_t bits = __float_as_uint(d2);
+    if (id != kEmptyId && d2 <= __uint_as_float(max_bits)) L.insert(((unsigned long long)bits << 32) | id, ref);
+    b = (b == head) ? ovf : __ldg(m.next + b);
+  }
+}
+
+// Search result, valid in lanes gl < cnt of the group: key (d2 bits << 32 | id), ref (slot index).
+template <int G>
+__device__ __forceinline__ void merge_top(const Group<G>& g, TopList& L, unsigned long long& okey, uint32_t& oref, int& cnt) {
+  okey = ~0ull;
+  oref = kNone;
+  cnt = 0;
+#pragma unroll
+  for (int j = 0; j < kK; ++j) {
+    unsigned long long k = L.k0;
+    uint32_t r = L.r0;
+#pragma unroll
+    for (int off = G / 2; off >= 1; off >>= 1) {
+      const unsigned long long ok = __shfl_xor_sync(g.mask, k, off);
+      const uint32_t orf = __shfl_xor_sync(g.mask, r, off);
+      if (ok < k) {
+        k = ok;
+        r = orf;
+      }
+    }
+    if (k != ~0ull) ++cnt;
+    if (L.k0 == k && k != ~0ull) L.pop();  // ids are unique: exactly one lane owns the minimum
+    if (g.gl == j) {
+      okey = k;
+      oref = r;
+    }
+  }
+}
+
+template <int G>
+__device__ void knn_search(const MapView& m, const Group<G>& g, float qx, float qy, float qz, float max_d2,
+                           unsigned long long& okey, uint32_t& oref, int& cnt) {
+  const float h = m.cell_size;
+  const int cx = vox_of(qx, m.ds) >> m.cell_shift, cy = vox_of(qy, m.ds) >> m.cell_shift, cz = vox_of(qz, m.ds) >> m.cell_shift;
+  const uint32_t max_bits = __float_as_uint(max_d2);
+  TopList L;
+  L.clear();
+
+  // ---- ring 1: 27 cells, probes issued up front -------------------------------------------------
+  constexpr int NR = (27 + G - 1) / G;
+  unsigned long long keys[NR];
+  uint32_t slot[NR];
+  uint4 raw[NR];
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    const int idx = g.gl + r * G;
+    const int dz = idx / 9, dy = (idx / 3) % 3, dx = idx % 3;
+    keys[r] = pack3(cx + dx - 1, cy + dy - 1, cz + dz - 1);
+    slot[r] = hash64(keys[r]) & m.mask;
+    if (idx < 27) raw[r] = __ldg(reinterpret_cast<const uint4*>(m.table + slot[r]));
+    else raw[r] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, kNone, kNone);
+  }
+#pragma unroll
+  for (int r = 0; r < NR; ++r) {
+    unsigned long long ek = ((unsigned long long)raw[r].y << 32) | raw[r].x;
+    while (ek != keys[r] && ek != kEmptyKey) {  // linear probing past a collision
+      slot[r] = (slot[r] + 1) & m.mask;
+      raw[r] = __ldg(reinterpret_cast<const uint4*>(m.table + slot[r]));
+      ek = ((unsigned long long)raw[r].y << 32) | raw[r].x;
+    }
+    const bool hit = (ek == keys[r]) && (g.gl + r * G < 27);
+    unsigned hits = g.ballot(hit);
+    while (hits) {
+      // hand one chain to each sub-group of 8 lanes
+      uint32_t head = kNone, ovf = kNone;
+      unsigned rest = hits;
+#pragma unroll
+      for (int s = 0; s < Group<G>::kSub; ++s) {
+        const int src = rest ? (__ffs(rest) - 1) : 0;
+        const uint32_t hh = g.shfl(raw[r].z, src), oo = g.shfl(raw[r].w, src);
+        if (rest && (g.gl / kSlots) == s) {
+          head = hh;
+          ovf = oo;
+        }
+        if (rest) rest &= rest - 1;
+      }
+      hits = rest;
+      scan_chain<G>(m, g, head, ovf, qx, qy, qz, max_bits, L);
+    }
+  }
+  merge_top<G>(g, L, okey, oref, cnt);
+
+  // ---- rings 2.. : only while the answer could still change ------------------------------------------
+  const float fx = qx - (float)cx * h, fy = qy - (float)cy * h, fz = qz - (float)cz * h;  // offset inside the centre cell
+  const float lo = fminf(fminf(fx, fy), fz), hi = fminf(fminf(h - fx, h - fy), h - fz);
+  const float edge = fmaxf(fminf(lo, hi), 0.f);  // distance to the nearest face of the centre cell
+  const int max_ring = (int)ceilf(sqrtf(max_d2) / h) + 1;
+  for (int ring = 2; ring <= max_ring; ++ring) {
+    // everything within `reach` of the query has been seen
+    const float reach = ((float)(ring - 1) * h + edge) * 0.9999f;
+    const unsigned long long k5 = g.shfl(okey, kK - 1);
+    const float tau = (cnt == kK) ? __uint_as_float((uint32_t)(k5 >> 32)) : max_d2;
+    if (tau < reach * reach) break;
+    // re-seed the private lists with the current answer
+    L.clear();
+    if (g.gl < cnt) L.insert(okey, oref);
+    const int side = 2 * ring + 1, total = side * side * side;
+    for (int idx0 = 0; idx0 < total; idx0 += G) {
+      const int idx = idx0 + g.gl;
+      const int dz = idx / (side * side) - ring, dy = (idx / side) % side - ring, dx = idx % side - ring;
+      bool want = idx < total && max(max(abs(dx), abs(dy)), abs(dz)) == ring;
+      if (want) want = cell_box_d2(qx, qy, qz, cx + dx, cy + dy, cz + dz, h) * 0.9999f <= tau;
+      HashEntry e;
+      e.key = kEmptyKey;
+      e.head = e.ovf = kNone;
+      unsigned long long key = 0;
+      if (want) {
+        key = pack3(cx + dx, cy + dy, cz + dz);
+        e = table_find(m, key);
+      }
+      unsigned hits = g.ballot(want && e.key == key);
+      while (hits) {
+        uint32_t head = kNone, ovf = kNone;
+        unsigned rest = hits;
+#pragma unroll
+        for (int s = 0; s < Group<G>::kSub; ++s) {
+          const int src = rest ? (__ffs(rest) - 1) : 0;
+          const uint32_t hh = g.shfl(e.head, src), oo = g.shfl(e.ovf, src);
+          if (rest && (g.gl / kSlots) == s) {
+            head = hh;
+            ovf = oo;
+          }
+          if (rest) rest &= rest - 1;
+        }
+        hits = rest;
+        scan_chain<G>(m, g, head, ovf, qx, qy, qz, max_bits, L);
+      }
+    }
+    merge_top<G>(g, L, okey, oref, cnt);
+  }
+}
+
+}  // namespace lio

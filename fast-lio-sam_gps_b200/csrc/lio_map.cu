@@ -1,0 +1,439 @@
+// GPU-resident map: voxel-hashed point store with ikd-Tree's observable semantics
+// (Build, Add_Points with/without downsample, Delete_Point_Boxes, size, flatten) — kernel K2 of SURVEY.md §2.2.
+// Reference behaviour: third_party/FAST_LIO/include/ikd-Tree/ikd_Tree.cpp (absent submodule).
+//
+// Downsample-on-insert is order dependent in the reference (points are processed one by one).  The
+// kernels below reproduce the RESULT of that sequential process without a sort:
+//   scan   : every batch point finds the best existing point of its filter_size_map voxel
+//            (min (dist-to-centre, id)) and takes part in a per-voxel atomicMin arbitration among the
+//            batch (min dist, ties -> later point, exactly what "new point wins ties" yields sequentially);
+//   commit : the batch winner of a voxel replaces the existing points when its distance is <= theirs,
+//            otherwise the voxel is collapsed to its best existing point.
+#include <algorithm>
+#include <cstring>
+#include "lio_ctx.h"
+
+namespace lio {
+
+namespace {
+
+__device__ __forceinline__ uint32_t batch_n(uint32_t n_max, const uint32_t* n_dev) {
+  if (!n_dev) return n_max;
+  uint32_t n = *n_dev;
+  return n < n_max ? n : n_max;
+}
+
+// ---- pass 1: make sure the cell of every batch point exists -----------------------------------
+__global__ void k_cells_ensure(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
+                               uint32_t* __restrict__ ent) {
+  const uint32_t n = batch_n(n_max, n_dev);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 p = pts[i];
+    const int cx = vox_of(p.x, m.ds) >> m.cell_shift, cy = vox_of(p.y, m.ds) >> m.cell_shift,
+              cz = vox_of(p.z, m.ds) >> m.cell_shift;
+    const unsigned long long key = pack3(cx, cy, cz);
+    uint32_t s = hash64(key) & m.mask;
+    uint32_t found = kNone;
+    for (uint32_t probes = 0; probes <= m.mask; ++probes) {
+      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&m.table[s].key);
+      if (cur == kEmptyKey) cur = atomicCAS(&m.table[s].key, kEmptyKey, key);
+      if (cur == kEmptyKey) {  // this thread created the cell: give it a head bucket
+        uint32_t b = atomicAdd(&m.ctr->pool_top, 1u);
+        if (b >= m.pool_cap) {
+          atomicOr(&m.ctr->error, kErrPoolFull);
+          b = 0;
+        }
+        m.table[s].head = b;
+        atomicAdd(&m.ctr->n_cells, 1u);
+        found = s;
+        break;
+      }
+      if (cur == key) {
+        found = s;
+        break;
+      }
+      s = (s + 1) & m.mask;
+    }
+    if (found == kNone) atomicOr(&m.ctr->error, kErrHashFull);
+    ent[i] = found;
+  }
+}
+
+// claim a free slot in the chain of hash entry `ei` and store the point there
+__device__ bool claim_slot(const MapView& m, uint32_t ei, float x, float y, float z, uint32_t id) {
+  HashEntry* e = m.table + ei;
+  const uint32_t head = e->head;
+  uint32_t b = head, spare = kNone;
+  while (true) {
+    float4* s = m.slots + (size_t)b * kSlots;
+#pragma unroll
+    for (int j = 0; j < kSlots; ++j) {
+      uint32_t* w = reinterpret_cast<uint32_t*>(&s[j].w);
+      if (*reinterpret_cast<volatile uint32_t*>(w) == kEmptyId && atomicCAS(w, kEmptyId, id) == kEmptyId) {
+        s[j].x = x;
+        s[j].y = y;
+        s[j].z = z;
+        return true;
+      }
+    }
+    uint32_t* link = (b == head) ? &e->ovf : &m.next[b];
+    uint32_t nb = *reinterpret_cast<volatile uint32_t*>(link);
+    if (nb == kNone) {
+      if (spare == kNone) {
+        spare = atomicAdd(&m.ctr->pool_top, 1u);
+        if (spare >= m.pool_cap) {
+          atomicOr(&m.ctr->error, kErrPoolFull);
+          return false;
+        }
+      }
+      const uint32_t prev = atomicCAS(link, kNone, spare);
+      if (prev == kNone) {
+        nb = spare;
+        spare = kNone;
+      } else {
+        nb = prev;  // somebody else linked first; keep the spare for the next tail
+      }
+    }
+    b = nb;
+  }
+}
+
+// ---- Add_Points(points, false) -----------------------------------------------------------------
+__global__ void k_insert_plain(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
+                               const uint32_t* __restrict__ ent) {
+  const uint32_t n = batch_n(n_max, n_dev);
+  const uint32_t base = m.ctr->next_id;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t ei = ent[i];
+    if (ei == kNone) continue;
+    const float4 p = pts[i];
+    if (claim_slot(m, ei, p.x, p.y, p.z, base + i)) atomicAdd(&m.ctr->live, 1);
+  }
+}
+
+__device__ __forceinline__ void voxel_centre(int kx, int ky, int kz, float ds, float& mx, float& my, float& mz) {
+  const float minx = (float)kx * ds, miny = (float)ky * ds, minz = (float)kz * ds;
+  const float maxx = minx + ds, maxy = miny + ds, maxz = minz + ds;
+  mx = minx + (maxx - minx) / 2.0f;
+  my = miny + (maxy - miny) / 2.0f;
+  mz = minz + (maxz - minz) / 2.0f;
+}
+
+// ---- Add_Points(points, true), phase "scan" (read-only on the point store) ----------------------
+__global__ void k_ds_scan(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
+                          const uint32_t* __restrict__ ent, unsigned long long* vox_keys, unsigned long long* vox_best,
+                          uint32_t vox_mask, uint32_t* __restrict__ tslot, unsigned long long* __restrict__ ebest,
+                          uint32_t* __restrict__ ecnt) {
+  const uint32_t n = batch_n(n_max, n_dev);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t ei = ent[i];
+    tslot[i] = kNone;
+    if (ei == kNone) continue;
+    const float4 p = pts[i];
+    const int kx = vox_of(p.x, m.ds), ky = vox_of(p.y, m.ds), kz = vox_of(p.z, m.ds);
+    float mx, my, mz;
+    voxel_centre(kx, ky, kz, m.ds, mx, my, mz);
+    // best existing point of this voxel
+    unsigned long long best = ~0ull;
+    uint32_t cnt = 0;
+    const HashEntry e = m.table[ei];
+    for (uint32_t b = e.head; b != kNone; b = chain_next(m, e.head, e.ovf, b)) {
+      const float4* s = m.slots + (size_t)b * kSlots;
+#pragma unroll
+      for (int j = 0; j < kSlots; ++j) {
+        const float4 q = s[j];
+        const uint32_t id = __float_as_uint(q.w);
+        if (id == kEmptyId) continue;
+        if (vox_of(q.x, m.ds) != kx || vox_of(q.y, m.ds) != ky || vox_of(q.z, m.ds) != kz) continue;
+        ++cnt;
+        const unsigned long long k = key64(sqdist3(q.x, q.y, q.z, mx, my, mz), id);
+        if (k < best) best = k;
+      }
+    }
+    ebest[i] = best;
+    ecnt[i] = cnt;
+    // batch arbitration: min distance, ties -> the LATER batch point
+    const unsigned long long vkey = pack3(kx, ky, kz);
+    uint32_t s = hash64(vkey) & vox_mask;
+    while (true) {
+      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&vox_keys[s]);
+      if (cur == kEmptyKey) cur = atomicCAS(&vox_keys[s], kEmptyKey, vkey);
+      if (cur == kEmptyKey || cur == vkey) break;
+      s = (s + 1) & vox_mask;
+    }
+    const float d = sqdist3(p.x, p.y, p.z, mx, my, mz);
+    atomicMin(&vox_best[s], ((unsigned long long)__float_as_uint(d) << 32) | (0xFFFFFFFFu - i));
+    tslot[i] = s;
+  }
+}
+
+// remove the pre-existing points of voxel (kx,ky,kz) from the chain of entry e, except `keep`
+__device__ void erase_voxel(const MapView& m, const HashEntry& e, int kx, int ky, int kz, uint32_t base_id, uint32_t keep) {
+  for (uint32_t b = e.head; b != kNone; b = chain_next(m, e.head, e.ovf, b)) {
+    float4* s = m.slots + (size_t)b * kSlots;
+#pragma unroll
+    for (int j = 0; j < kSlots; ++j) {
+      uint32_t* w = reinterpret_cast<uint32_t*>(&s[j].w);
+      const uint32_t id = *reinterpret_cast<volatile uint32_t*>(w);
+      if (id == kEmptyId || id >= base_id || id == keep) continue;  // only points that predate this batch
+      const float x = *reinterpret_cast<volatile float*>(&s[j].x), y = *reinterpret_cast<volatile float*>(&s[j].y),
+                  z = *reinterpret_cast<volatile float*>(&s[j].z);
+      if (vox_of(x, m.ds) != kx || vox_of(y, m.ds) != ky || vox_of(z, m.ds) != kz) continue;
+      atomicCAS(w, id, kEmptyId);  // a slot that was recycled meanwhile carries another id and is left alone
+    }
+  }
+}
+
+// ---- Add_Points(points, true), phase "commit" ---------------------------------------------------
+__global__ void k_ds_commit(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
+                            const uint32_t* __restrict__ ent, const unsigned long long* __restrict__ vox_best,
+                            const uint32_t* __restrict__ tslot, const unsigned long long* __restrict__ ebest,
+                            const uint32_t* __restrict__ ecnt) {
+  const uint32_t n = batch_n(n_max, n_dev);
+  const uint32_t base = m.ctr->next_id;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t ts = tslot[i];
+    if (ts == kNone) continue;
+    const float4 p = pts[i];
+    const int kx = vox_of(p.x, m.ds), ky = vox_of(p.y, m.ds), kz = vox_of(p.z, m.ds);
+    float mx, my, mz;
+    voxel_centre(kx, ky, kz, m.ds, mx, my, mz);
+    const uint32_t dbits = __float_as_uint(sqdist3(p.x, p.y, p.z, mx, my, mz));
+    if (vox_best[ts] != (((unsigned long long)dbits << 32) | (0xFFFFFFFFu - i))) continue;  // not the voxel's winner
+    const uint32_t ei = ent[i];
+    const HashEntry e = m.table[ei];
+    const unsigned long long eb = ebest[i];
+    const uint32_t ec = ecnt[i];
+    if (ec == 0 || dbits <= (uint32_t)(eb >> 32)) {
+      if (ec) erase_voxel(m, e, kx, ky, kz, base, kEmptyId);
+      if (claim_slot(m, ei, p.x, p.y, p.z, base + i)) {
+        atomicAdd(&m.ctr->live, 1 - (int)ec);
+        atomicAdd(&m.ctr->batch_alive, 1u);
+      }
+    } else if (ec > 1) {
+      erase_voxel(m, e, kx, ky, kz, base, (uint32_t)eb);
+      atomicAdd(&m.ctr->live, -(int)(ec - 1));
+    }
+  }
+}
+
+__global__ void k_advance_ids(MapCounters* ctr, uint32_t n_max, const uint32_t* n_dev) {
+  ctr->next_id += batch_n(n_max, n_dev);
+}
+__global__ void k_reset_batch(MapCounters* ctr) { ctr->batch_alive = 0; }
+
+// ---- Delete_Point_Boxes --------------------------------------------------------------------------
+__global__ void k_delete_boxes(MapView m, const float* __restrict__ boxes, int nb) {
+  const uint32_t top = min(m.ctr->pool_top, m.pool_cap);
+  const size_t total = (size_t)top * kSlots;
+  uint32_t removed = 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 q = m.slots[i];
+    if (__float_as_uint(q.w) == kEmptyId) continue;
+    bool hit = false;
+    for (int b = 0; b < nb && !hit; ++b) {
+      const float* bx = boxes + 6 * b;
+      hit = q.x >= bx[0] && q.x < bx[3] && q.y >= bx[1] && q.y < bx[4] && q.z >= bx[2] && q.z < bx[5];
+    }
+    if (hit) {
+      reinterpret_cast<uint32_t*>(&m.slots[i].w)[0] = kEmptyId;
+      ++removed;
+    }
+  }
+  if (removed) {
+    atomicAdd(&m.ctr->deleted, removed);
+    atomicAdd(&m.ctr->live, -(int)removed);
+  }
+}
+__global__ void k_reset_deleted(MapCounters* ctr) { ctr->deleted = 0; }
+
+// ---- flatten ---------------------------------------------------------------------------------------
+__global__ void k_export(MapView m, float4* __restrict__ out, uint32_t cap, uint32_t* cursor) {
+  const uint32_t top = min(m.ctr->pool_top, m.pool_cap);
+  const size_t total = (size_t)top * kSlots;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 q = m.slots[i];
+    if (__float_as_uint(q.w) == kEmptyId) continue;
+    const uint32_t pos = atomicAdd(cursor, 1u);
+    if (pos < cap) out[pos] = q;
+  }
+}
+
+uint32_t next_pow2(uint64_t v) {
+  uint64_t p = 1;
+  while (p < v) p <<= 1;
+  return (uint32_t)std::min<uint64_t>(p, 1ull << 31);
+}
+
+int grid_for(const lio_ctx* c, uint32_t n, int block) {
+  const int want = (int)((n + block - 1) / block);
+  return std::max(1, std::min(want, c->n_sms * 16));
+}
+
+}  // namespace
+
+int map_alloc(lio_ctx* c) {
+  const lio_config& cfg = c->cfg;
+  MapView& m = c->map;
+  m.ds = cfg.filter_size_map;
+  int mult = cfg.cell_mult > 0 ? cfg.cell_mult : 2;
+  int shift = 0;
+  while ((1 << shift) < mult) ++shift;
+  if ((1 << shift) != mult) {
+    set_error("cell_mult must be a power of two (got %d)", mult);
+    return LIO_E_ARG;
+  }
+  m.cell_shift = shift;
+  m.cell_size = m.ds * (float)mult;
+  const uint64_t cells = cfg.max_cells ? cfg.max_cells : cfg.max_points;
+  c->table_cap = next_pow2(std::max<uint64_t>(1024, cells * 2));
+  m.mask = c->table_cap - 1;
+  // one head bucket per cell plus overflow room for cells holding more than kSlots points
+  m.pool_cap = (uint32_t)std::min<uint64_t>(cells + cfg.max_points / kSlots + 1024, 0x7FFFFFFFull);
+  LIO_CUDA(cudaMalloc(&m.table, sizeof(HashEntry) * (size_t)c->table_cap));
+  LIO_CUDA(cudaMalloc(&m.slots, sizeof(float4) * kSlots * (size_t)m.pool_cap));
+  LIO_CUDA(cudaMalloc(&m.next, sizeof(uint32_t) * (size_t)m.pool_cap));
+  LIO_CUDA(cudaMalloc(&m.ctr, sizeof(MapCounters)));
+  LIO_CUDA(cudaMalloc(&c->boxes_dev, sizeof(float) * 6 * 64));
+  LIO_CUDA(cudaMemsetAsync(m.ctr, 0, sizeof(MapCounters), c->stream));
+  return map_clear(c);
+}
+
+void map_free(lio_ctx* c) {
+  MapView& m = c->map;
+  cudaFree(m.table);
+  cudaFree(m.slots);
+  cudaFree(m.next);
+  cudaFree(m.ctr);
+  cudaFree(c->boxes_dev);
+  cudaFree(c->batch_pts);
+  cudaFree(c->batch_ent);
+  cudaFree(c->batch_tslot);
+  cudaFree(c->batch_ebest);
+  cudaFree(c->batch_ecnt);
+  cudaFree(c->vox_keys);
+  cudaFree(c->vox_best);
+  m = MapView{};
+}
+
+// empties the store; the id counter keeps running (the oracle's Build does the same)
+int map_clear(lio_ctx* c) {
+  MapView& m = c->map;
+  LIO_CUDA(cudaMemsetAsync(m.table, 0xFF, sizeof(HashEntry) * (size_t)c->table_cap, c->stream));
+  LIO_CUDA(cudaMemsetAsync(m.slots, 0xFF, sizeof(float4) * kSlots * (size_t)m.pool_cap, c->stream));
+  LIO_CUDA(cudaMemsetAsync(m.next, 0xFF, sizeof(uint32_t) * (size_t)m.pool_cap, c->stream));
+  // keep next_id and the sticky error word, zero the rest
+  LIO_CUDA(cudaMemsetAsync(&m.ctr->pool_top, 0, sizeof(uint32_t) * 3, c->stream));
+  return LIO_OK;
+}
+
+int map_ensure_batch(lio_ctx* c, uint32_t n) {
+  if (n <= c->batch_cap) return LIO_OK;
+  cudaFree(c->batch_pts);
+  cudaFree(c->batch_ent);
+  cudaFree(c->batch_tslot);
+  cudaFree(c->batch_ebest);
+  cudaFree(c->batch_ecnt);
+  cudaFree(c->vox_keys);
+  cudaFree(c->vox_best);
+  c->batch_cap = 0;
+  const uint32_t cap = std::max<uint32_t>(n, 1024);
+  LIO_CUDA(cudaMalloc(&c->batch_pts, sizeof(float4) * (size_t)cap));
+  LIO_CUDA(cudaMalloc(&c->batch_ent, sizeof(uint32_t) * (size_t)cap));
+  LIO_CUDA(cudaMalloc(&c->batch_tslot, sizeof(uint32_t) * (size_t)cap));
+  LIO_CUDA(cudaMalloc(&c->batch_ebest, sizeof(unsigned long long) * (size_t)cap));
+  LIO_CUDA(cudaMalloc(&c->batch_ecnt, sizeof(uint32_t) * (size_t)cap));
+  c->vox_cap = next_pow2((uint64_t)cap * 2);
+  LIO_CUDA(cudaMalloc(&c->vox_keys, sizeof(unsigned long long) * (size_t)c->vox_cap));
+  LIO_CUDA(cudaMalloc(&c->vox_best, sizeof(unsigned long long) * (size_t)c->vox_cap));
+  c->batch_cap = cap;
+  return LIO_OK;
+}
+
+// Add_Points on a device-resident batch.  n_dev (optional) holds the actual count (<= n_max).
+int map_add_device(lio_ctx* c, const float4* pts, uint32_t n_max, const uint32_t* n_dev, bool downsample) {
+  if (n_max == 0) return LIO_OK;
+  int rc = map_ensure_batch(c, n_max);
+  if (rc) return rc;
+  const int block = 256, grid = grid_for(c, n_max, block);
+  MapView& m = c->map;
+  timer_begin(c, T_INSERT);
+  k_cells_ensure<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent);
+  if (!downsample) {
+    k_insert_plain<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent);
+    c->launches += 2;
+  } else {
+    // the arbitration table only needs to cover this batch
+    const uint32_t vcap = std::min<uint32_t>(c->vox_cap, next_pow2((uint64_t)std::max<uint32_t>(n_max, 512) * 2));
+    cudaMemsetAsync(c->vox_keys, 0xFF, sizeof(unsigned long long) * (size_t)vcap, c->stream);
+    cudaMemsetAsync(c->vox_best, 0xFF, sizeof(unsigned long long) * (size_t)vcap, c->stream);
+    k_reset_batch<<<1, 1, 0, c->stream>>>(m.ctr);
+    k_ds_scan<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent, c->vox_keys, c->vox_best, vcap - 1,
+                                             c->batch_tslot, c->batch_ebest, c->batch_ecnt);
+    k_ds_commit<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent, c->vox_best, c->batch_tslot,
+                                               c->batch_ebest, c->batch_ecnt);
+    c->launches += 4;
+  }
+  k_advance_ids<<<1, 1, 0, c->stream>>>(m.ctr, n_max, n_dev);
+  c->launches += 1;
+  timer_end(c);
+  LIO_CUDA(cudaGetLastError());
+  return LIO_OK;
+}
+
+int map_delete_boxes(lio_ctx* c, const float* boxes_host, int nb) {
+  if (nb <= 0) return LIO_OK;
+  if (nb > 64) {
+    set_error("at most 64 boxes per call (got %d)", nb);
+    return LIO_E_ARG;
+  }
+  LIO_CUDA(cudaMemcpyAsync(c->boxes_dev, boxes_host, sizeof(float) * 6 * nb, cudaMemcpyHostToDevice, c->stream));
+  k_reset_deleted<<<1, 1, 0, c->stream>>>(c->map.ctr);
+  k_delete_boxes<<<c->n_sms * 8, 256, 0, c->stream>>>(c->map, c->boxes_dev, nb);
+  c->launches += 2;
+  LIO_CUDA(cudaGetLastError());
+  // the host copy of `boxes_host` may go away once we return
+  LIO_CUDA(cudaStreamSynchronize(c->stream));
+  return LIO_OK;
+}
+
+int map_read_counters(lio_ctx* c, MapCounters* out) {
+  LIO_CUDA(cudaMemcpyAsync(out, c->map.ctr, sizeof(MapCounters), cudaMemcpyDeviceToHost, c->stream));
+  LIO_CUDA(cudaStreamSynchronize(c->stream));
+  if (out->error) {
+    set_error("map capacity exhausted (%s%s): raise lio_config.max_points / max_cells",
+              (out->error & kErrHashFull) ? "hash table " : "", (out->error & kErrPoolFull) ? "bucket pool" : "");
+    return LIO_E_CAPACITY;
+  }
+  return LIO_OK;
+}
+
+int map_export(lio_ctx* c, std::vector<float4>& out) {
+  MapCounters ctr;
+  int rc = map_read_counters(c, &ctr);
+  if (rc) return rc;
+  const uint32_t live = ctr.live > 0 ? (uint32_t)ctr.live : 0;
+  out.resize(live);
+  if (!live) return LIO_OK;
+  float4* dev = nullptr;
+  uint32_t* cursor = nullptr;
+  LIO_CUDA(cudaMalloc(&dev, sizeof(float4) * (size_t)live));
+  LIO_CUDA(cudaMalloc(&cursor, sizeof(uint32_t)));
+  cudaMemsetAsync(cursor, 0, sizeof(uint32_t), c->stream);
+  k_export<<<c->n_sms * 8, 256, 0, c->stream>>>(c->map, dev, live, cursor);
+  c->launches += 1;
+  cudaMemcpyAsync(out.data(), dev, sizeof(float4) * (size_t)live, cudaMemcpyDeviceToHost, c->stream);
+  cudaError_t e = cudaStreamSynchronize(c->stream);
+  cudaFree(dev);
+  cudaFree(cursor);
+  if (!cuda_ok(e, "map_export")) return LIO_E_CUDA;
+  std::sort(out.begin(), out.end(), [](const float4& a, const float4& b) {
+    uint32_t ia, ib;
+    std::memcpy(&ia, &a.w, 4);
+    std::memcpy(&ib, &b.w, 4);
+    return ia < ib;
+  });
+  return LIO_OK;
+}
+
+}  // namespace lio

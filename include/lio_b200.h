@@ -1,0 +1,123 @@
+/*
+ * lio_b200.h — C-ABI of the B200-native FAST-LIO measurement path (seam B1).
+ *
+ * Replaces, behind the unchanged `h_dyn_share` callback / esekfom state layout:
+ *   third_party/FAST_LIO/src/laserMapping.cpp        h_share_model, map_incremental, lasermap_fov_segment
+ *   third_party/FAST_LIO/include/common_lib.h        esti_plane
+ *   third_party/FAST_LIO/include/ikd-Tree/ikd_Tree.h Build, Nearest_Search, Add_Points, Delete_Point_Boxes
+ *   third_party/FAST_LIO/include/IKFoM_toolkit/esekfom/esekfom.hpp  update_iterated_dyn_share_modified
+ * The FAST_LIO submodule is absent from the reference mount (/root/reference/.SUBMODULES.json:9-15),
+ * so no file:line can be cited for these; the verified anchors are the parameter names/values in
+ * /root/reference/third_party/fastlio_config_launch/kitti.launch:6-12 and kitti.yaml:16-22.
+ *
+ * Plain C: pointers and sizes only.  All entry points return LIO_OK (0) or a negative LIO_E_* code;
+ * nothing throws.  One host thread at a time per handle; each handle owns a CUDA stream.
+ * There is NO CPU fallback: every compute entry point fails with LIO_E_CUDA when no sm_100 device is usable.
+ */
+#ifndef LIO_B200_H
+#define LIO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LIO_OK 0
+#define LIO_E_CUDA (-1)     /* CUDA runtime error (no device, launch failure, ...) */
+#define LIO_E_ARG (-2)      /* bad argument */
+#define LIO_E_CAPACITY (-3) /* map hash table or bucket pool exhausted */
+#define LIO_E_STATE (-4)    /* call order violated (e.g. h_share before scan upload) */
+
+#define LIO_NUM_MATCH 5       /* NUM_MATCH_POINTS */
+#define LIO_STATE_DOUBLES 36  /* pos3 | rot 3x3 row-major | offset_R_L_I 3x3 | offset_T_L_I 3 | vel3 | bg3 | ba3 | grav3 */
+#define LIO_ERR_DOF 23        /* esekfom error-state dimension of state_ikfom */
+
+typedef struct lio_ctx lio_ctx; /* opaque: GPU map + current scan + stream */
+
+typedef struct lio_config {
+  int device;            /* CUDA ordinal */
+  float filter_size_map; /* ikd-Tree downsample size (kitti.launch:10: 0.5) */
+  int cell_mult;         /* hash cell = cell_mult x filter_size_map; power of two; 0 -> 2 */
+  uint32_t max_points;   /* capacity of the point store (bucket pool sized from it) */
+  uint32_t max_cells;    /* expected number of occupied hash cells; 0 -> max_points */
+  uint32_t max_scan;     /* largest scan (points) that will be uploaded */
+  float max_sqdist;      /* neighbour acceptance bound on the 5th squared distance (reference: 5) */
+  int extrinsic_est_en;  /* 0 -> Jacobian cols 6..11 are zero (kitti.yaml:22) */
+  double cube_side_length; /* kitti.launch:11 */
+  float det_range;         /* mapping/det_range */
+  void* stream;          /* optional external cudaStream_t; NULL -> the context creates its own */
+} lio_config;
+
+const char* lio_version(void);
+const char* lio_last_error(void); /* thread-local text of the last failure */
+int lio_device_count(void);
+
+int lio_ctx_create(const lio_config* cfg, lio_ctx** out);
+void lio_ctx_destroy(lio_ctx* ctx);
+int lio_ctx_sync(lio_ctx* ctx); /* wait for the stream; surfaces deferred LIO_E_CAPACITY */
+
+/* ---- map: replaces KD_TREE<PointType> ------------------------------------------------------------ */
+/* Build(points): clears the map, then plain-inserts n points (xyz, stride 3 floats, HOST memory).
+ * Every point handed to build/add gets id = running counter, in list order. */
+int lio_map_build(lio_ctx* ctx, const float* xyz, int n);
+/* Add_Points(points, downsample_on).  *net_new (optional) = points of this batch alive afterwards. */
+int lio_map_add(lio_ctx* ctx, const float* xyz, int n, int downsample_on, int* net_new);
+/* Delete_Point_Boxes: nb boxes of 6 floats (min xyz, max xyz), half-open.  *n_deleted optional. */
+int lio_map_delete_boxes(lio_ctx* ctx, const float* boxes, int nb, int* n_deleted);
+int lio_map_size(lio_ctx* ctx, int* n_live);
+/* flatten(): live points in ascending id; returns total live count in *n_total, copies min(cap, total). */
+int lio_map_export(lio_ctx* ctx, float* xyz, uint32_t* ids, int cap, int* n_total);
+/* Nearest_Search, batched: n queries (host xyz) -> k<=5 neighbours each within max_sqdist, ascending
+ * (sqdist, id).  Rows are padded with id 0xFFFFFFFF / d2 +inf.  pts (n*k*3) and cnt (n) optional. */
+int lio_map_knn(lio_ctx* ctx, const float* q_xyz, int n, int k, float max_sqdist, uint32_t* ids, float* d2, float* pts,
+                int* cnt);
+
+/* ---- scan + measurement model: replaces h_share_model -------------------------------------------- */
+/* feats_down_body: n points (xyz, stride 3 floats, HOST memory) -> device. Invalidates cached neighbours. */
+int lio_scan_upload(lio_ctx* ctx, const float* body_xyz, int n);
+/* Same, from a DEVICE pointer to n float4 (x,y,z,unused). */
+int lio_scan_set_device(lio_ctx* ctx, const void* body_xyzw_dev, int n);
+
+/* One call of h_share_model at `state` (LIO_STATE_DOUBLES).  redo_knn = ekfom_data.converge.
+ * Outputs (HOST): HTH[144] row-major = h_x^T h_x, HTz[12] = h_x^T h, *n_eff = effct_feat_num,
+ * *res_sum (optional) = sum |pd2| over selected points.  ekfom_data.valid == (*n_eff >= 1). */
+int lio_h_share(lio_ctx* ctx, const double* state, int redo_knn, double* HTH, double* HTz, int* n_eff, double* res_sum);
+/* Same evaluation, returning the dense per-point products so an adapter can fill the unchanged
+ * dyn_share_datastruct: sel[n], rows[n*12] (h_x row, zero where !sel), z[n] (h = -pd2).  All HOST, all optional. */
+int lio_h_share_rows(lio_ctx* ctx, const double* state, int redo_knn, uint8_t* sel, double* rows, double* z, int* n_eff);
+/* Per-point products of the last h_share call (HOST, each optional): world[n*3], nn_ids[n*5],
+ * nn_xyz[n*5*3], nn_cnt[n], sel[n], plane[n*4] = (a,b,c,pd2). */
+int lio_scan_get(lio_ctx* ctx, float* world, uint32_t* nn_ids, float* nn_xyz, int* nn_cnt, uint8_t* sel, float* plane);
+
+/* ---- esekfom::update_iterated_dyn_share_modified on (state, P) with the GPU measurement model ------ */
+/* state: in/out LIO_STATE_DOUBLES; P: in/out 23x23 row-major; R = LASER_POINT_COV; limit[23] = epsi.
+ * Optional traces (HOST): iter_states[(max_iter+1)*36], n_eff_trace[max_iter+1], knn_trace[max_iter+1].
+ * *iters_done = number of measurement-model calls made. */
+int lio_iekf_update(lio_ctx* ctx, double* state, double* P, double R, int max_iter, const double* limit,
+                    double* iter_states, int* n_eff_trace, int* knn_trace, int* iters_done);
+
+/* map_incremental() at the final state, entirely on the device (classification from the cached
+ * neighbours, then Add_Points(PointToAdd,true) and Add_Points(PointNoNeedDownsample,false)).
+ * Counts are optional; asking for them synchronises. */
+int lio_map_incremental(lio_ctx* ctx, const double* state, int flg_ekf_inited, int* n_add, int* n_nodown);
+/* lasermap_fov_segment(): slides the local-map cube around pos_lid[3]; boxes_out optional (3x6 floats). */
+int lio_fov_segment(lio_ctx* ctx, const double* pos_lid, float* boxes_out, int* n_boxes);
+
+/* manifold helpers of the host-side esekfom mirror (exported for tests and adapters) */
+void lio_boxplus(double* state, const double* dx23);
+void lio_boxminus(const double* a, const double* b, double* dx23);
+
+/* ---- measurement hooks (bench / profiling only) ------------------------------------------------------ */
+/* Mean device time (ms) of the named kernel family since the last reset, measured with CUDA events on the
+ * context stream when timing is enabled: "knn", "plane_reduce", "insert", "classify". */
+int lio_timing_enable(lio_ctx* ctx, int on);
+int lio_timing_get(lio_ctx* ctx, const char* name, double* mean_ms, int* launches);
+int lio_timing_reset(lio_ctx* ctx);
+/* number of kernels this context has launched since creation */
+int64_t lio_launch_count(lio_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIO_B200_H */
