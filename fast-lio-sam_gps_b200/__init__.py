@@ -293,7 +293,7 @@ class LioContext:
         return int(self.lib.lio_launch_count(self.h))
 
 
-def identity_state(pos=(0, 0, 0), rot=None, grav=(0, 0, -9.809)):
+def identity_state(pos=(0, 0, 0), rot=None, grav=(0.19614, -0.14711, -9.80593)):
     """LIO_STATE_DOUBLES vector: pos | rot | offset_R_L_I | offset_T_L_I | vel | bg | ba | grav."""
     s = np.zeros(STATE_DOUBLES)
     s[0:3] = pos

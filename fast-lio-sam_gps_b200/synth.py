@@ -184,7 +184,15 @@ def make_scan(scene, R, t, kind="vlp16", noise=0.02, seed=SEED + 2, phase=0.0, n
     return np.ascontiguousarray(pts)
 
 
-def make_state(R, t, grav=(0.0, 0.0, -9.809)):
+def default_grav():
+    """Gravity a few mrad off the S2 chart's pole: state_ikfom's S2 basis degenerates EXACTLY at
+    (0, 0, -9.809) (MTK S2_Bx takes its fallback branch there), which a real IMU initialisation never hits."""
+    g = np.array([0.02, -0.015, -1.0])
+    return g / np.linalg.norm(g) * 9.809
+
+
+def make_state(R, t, grav=None):
+    grav = default_grav() if grav is None else grav
     s = np.zeros(36)
     s[0:3] = t
     s[3:12] = np.asarray(R, float).reshape(9)

@@ -1,0 +1,321 @@
+"""GPU parity tests of the IEKF measurement path, called through the C-ABI (include/lio_b200.h).
+
+Bars (BASELINE.json north_star): kNN index sets and plane-validity masks bit-exact; H^T H / H^T z within
+1e-5 relative; per-iteration state updates within 1e-6 m / 1e-6 rad; trajectory divergence < 1 mm.
+The checker is the CPU oracle on identical seeded inputs.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-5  # north_star tolerance on H^T H / H^T z
+STATE_TOL = 1e-6  # m / rad per iteration
+
+
+def rel_err(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def pair(pkg, orc, small_world):
+    g = pkg.LioContext(0.5, max_points=1 << 19, max_scan=1 << 16)
+    o = orc.OracleLio(0.5, nthreads=0)
+    g.map_build(small_world["map"])
+    o.map_build(small_world["map"])
+    yield g, o
+    g.close()
+    o.close()
+
+
+def test_library_is_the_cuda_one(pkg):
+    lib = pkg.load_library()
+    assert b"sm_100a" in lib.lio_version()
+    assert lib.lio_device_count() >= 1
+
+
+def test_map_build_roundtrip(pair, small_world):
+    g, o = pair
+    assert g.map_size() == o.map_size() == len(small_world["map"])
+    xyz, ids = g.map_export()
+    assert np.array_equal(ids, np.arange(len(ids), dtype=np.uint32))
+    assert np.array_equal(xyz, small_world["map"])
+
+
+def test_knn_bit_exact(pair, small_world):
+    g, o = pair
+    rng = np.random.default_rng(7)
+    m = small_world["map"]
+    q = m[rng.integers(0, len(m), 20000)] + rng.normal(0, 0.4, (20000, 3)).astype(np.float32)
+    q = np.concatenate([q, rng.uniform(-90, 90, (2000, 3)).astype(np.float32), m[:2000]])  # far, and exact hits (d2 = 0)
+    for k in (5, 1, 3):
+        gi, gd, gp, gc = g.map_knn(q, k, 5.0)
+        oi, od, op, oc = o.map_knn(q, k, 5.0)
+        assert np.array_equal(gc, oc)
+        assert np.array_equal(gi, oi)
+        assert np.array_equal(gd, od)
+        assert np.array_equal(gp, op)
+    assert (gc < 3).any() and (gc == 3).any()  # both padded and full rows were exercised
+
+
+def test_knn_ring_expansion_is_exact(pkg, orc):
+    """Sparse map + large radius: the answer lies several hash cells away, so rings 2.. must be searched."""
+    rng = np.random.default_rng(8)
+    m = rng.uniform(-20, 20, (3000, 3)).astype(np.float32)
+    q = rng.uniform(-22, 22, (4000, 3)).astype(np.float32)
+    g = pkg.LioContext(0.5, max_points=1 << 14, max_scan=1024)
+    o = orc.OracleLio(0.5)
+    g.map_build(m)
+    o.map_build(m)
+    for r2 in (5.0, 30.0, 100.0):
+        gi, gd, _, gc = g.map_knn(q, 5, r2)
+        oi, od, _, oc = o.map_knn(q, 5, r2)
+        assert np.array_equal(gi, oi) and np.array_equal(gd, od) and np.array_equal(gc, oc)
+    g.close()
+
+
+def test_knn_ties_and_duplicates(pkg, orc):
+    pts = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1], [3, 0, 0], [1, 0, 0], [1, 0, 0]], np.float32)
+    g = pkg.LioContext(0.5, max_points=1024, max_scan=128)
+    o = orc.OracleLio(0.5)
+    g.map_build(pts)
+    o.map_build(pts)
+    q = np.array([[0, 0, 0], [1, 0, 0], [0.5, 0, 0]], np.float32)
+    gi, gd, _, _ = g.map_knn(q, 5, 5.0)
+    oi, od, _, _ = o.map_knn(q, 5, 5.0)
+    assert np.array_equal(gi, oi) and np.array_equal(gd, od)
+    assert gi[0].tolist() == [0, 1, 2, 3, 4]
+    g.close()
+
+
+@pytest.mark.parametrize("ext", [False, True])
+def test_h_share_parity(pkg, orc, small_world, ext):
+    w = small_world
+    g = pkg.LioContext(0.5, max_points=1 << 19, max_scan=1 << 16, extrinsic_est_en=ext)
+    o = orc.OracleLio(0.5, nthreads=0, extrinsic_est_en=ext)
+    g.map_build(w["map"])
+    o.map_build(w["map"])
+    g.scan_upload(w["scan"])
+    o.scan_upload(w["scan"])
+    st = w["start"].copy()
+    if ext:
+        st[21:24] = [0.05, -0.02, 0.1]
+    for redo, state in ((True, st), (False, w["truth"] if not ext else st), (True, w["truth"])):
+        gH, gz, gn, gr = g.h_share(state, redo)
+        oH, oz, on, orr = o.h_share(state, redo)
+        go, oo = g.scan_get(), o.scan_get()
+        assert np.array_equal(go["world"], oo["world"])
+        assert np.array_equal(go["nn_cnt"], oo["nn_cnt"])
+        assert np.array_equal(go["nn_ids"], oo["nn_ids"])  # kNN index sets: bit-exact
+        assert np.array_equal(go["nn_xyz"], oo["nn_xyz"])
+        assert np.array_equal(go["sel"], oo["sel"])  # plane-validity mask: bit-exact
+        s = oo["sel"] == 1
+        assert np.array_equal(go["plane"][s], oo["plane"][s])
+        assert gn == on and on > 1000
+        assert rel_err(gH, oH) < REL and rel_err(gz, oz) < REL
+        assert rel_err(gH, oH) < 1e-11  # same f64 rows, only the summation order differs
+        assert abs(gr - orr) <= 1e-9 * orr
+        assert np.array_equal(gH, gH.T)
+    g.close()
+
+
+def test_h_share_rows_fill_dyn_share(pair, small_world):
+    """lio_h_share_rows delivers what an adapter needs to fill the unchanged dyn_share_datastruct (h_x, h)."""
+    g, o = pair
+    w = small_world
+    g.scan_upload(w["scan"])
+    o.scan_upload(w["scan"])
+    sel, rows, z, n_eff = g.h_share_rows(w["start"], True)
+    oH, oz, on, _, hx, hz = o.h_share(w["start"], True, want_rows=True)
+    assert n_eff == on == sel.sum()
+    assert np.allclose(rows[sel == 1], hx, rtol=0, atol=1e-12)
+    assert np.allclose(z[sel == 1], hz, rtol=0, atol=0)
+    assert (rows[sel == 0] == 0).all()
+
+
+def test_iekf_update_parity(pair, synth, small_world):
+    g, o = pair
+    w = small_world
+    g.scan_upload(w["scan"])
+    o.scan_upload(w["scan"])
+    P0 = synth.default_cov()
+    gs, gP, gi = g.iekf_update(w["start"], P0, trace=True)
+    os_, oP, oi = o.iekf_update(w["start"], P0, trace=True)
+    assert gi["iters"] == oi["iters"]
+    assert np.array_equal(gi["n_eff"], oi["n_eff"]) and np.array_equal(gi["knn"], oi["knn"])
+    assert np.abs(gi["states"] - oi["states"]).max() < STATE_TOL  # per-iteration state updates
+    assert np.abs(gs - os_).max() < STATE_TOL
+    assert np.abs(gP - oP).max() < 1e-9
+    assert np.linalg.norm(gs[:3] - w["truth"][:3]) < 0.01
+
+
+def test_map_add_downsample_parity(pkg, orc):
+    rng = np.random.default_rng(9)
+    g = pkg.LioContext(0.5, max_points=1 << 16, max_scan=1024)
+    o = orc.OracleLio(0.5)
+    base = rng.uniform(-6, 6, (5000, 3)).astype(np.float32)
+    g.map_build(base)
+    o.map_build(base)
+    for rnd in range(4):
+        # dense batches: many points per voxel, voxels that already hold several points, exact duplicates
+        batch = rng.uniform(-6.5, 6.5, (4000, 3)).astype(np.float32)
+        batch[100:110] = batch[0:10]
+        down = rnd != 2
+        gnet = g.map_add(batch, down)
+        onet, _ = o.map_add(batch, down)
+        assert gnet == onet
+        gx, gi = g.map_export()
+        ox, oi = o.map_export()
+        assert g.map_size() == o.map_size() == len(oi)
+        assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
+    q = rng.uniform(-6, 6, (3000, 3)).astype(np.float32)
+    a, b = g.map_knn(q, 5, 5.0), o.map_knn(q, 5, 5.0)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    g.close()
+
+
+def test_map_delete_boxes_parity(pkg, orc):
+    rng = np.random.default_rng(10)
+    g = pkg.LioContext(0.5, max_points=1 << 16, max_scan=1024)
+    o = orc.OracleLio(0.5)
+    base = rng.uniform(-8, 8, (20000, 3)).astype(np.float32)
+    g.map_build(base)
+    o.map_build(base)
+    boxes = np.array([[-2, -2, -2, 1, 3, 2], [4, 4, 4, 9, 9, 9], [-9, -9, -9, -8.5, 9, 9]], np.float32)
+    assert g.map_delete_boxes(boxes) == o.map_delete_boxes(boxes) > 0
+    assert g.map_delete_boxes(boxes) == 0
+    gx, gi = g.map_export()
+    ox, oi = o.map_export()
+    assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
+    # freed slots are reused by later inserts and searches stay exact
+    more = rng.uniform(-3, 3, (3000, 3)).astype(np.float32)
+    assert g.map_add(more, True) == o.map_add(more, True)[0]
+    q = rng.uniform(-8, 8, (3000, 3)).astype(np.float32)
+    a, b = g.map_knn(q, 5, 5.0), o.map_knn(q, 5, 5.0)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    g.close()
+
+
+def test_sequence_with_map_growth_ate(pkg, orc, synth):
+    """Config-1/3 shaped slice: scans along a street, IEKF update + map_incremental every scan, local-map cube moving.
+    GPU and oracle run independently; live map sets must stay equal and the trajectories within 1 mm."""
+    scene = synth.make_scene(half_extent=60.0)
+    poses = synth.street_poses(12, scene, step=0.7)
+    g = pkg.LioContext(0.5, max_points=1 << 19, max_scan=1 << 16, cube_side_length=100.0, det_range=20.0)
+    o = orc.OracleLio(0.5, nthreads=0, cube_side_length=100.0, det_range=20.0)
+    R0, t0 = poses[0]
+    first = synth.make_scan(scene, R0, t0, kind="vlp16", seed=100)
+    world0 = (first.astype(np.float64) @ R0.T + t0).astype(np.float32)
+    g.map_build(world0)
+    o.map_build(world0)
+    gs = os_ = synth.make_state(R0, t0)
+    gP = oP = synth.default_cov()
+    Q = np.eye(23) * 1e-5
+    traj_g, traj_o = [], []
+    for i, (R, t) in enumerate(poses[1:], 1):
+        kind = "avia" if i % 2 else "vlp16"
+        scan = synth.make_scan(scene, R, t, kind=kind, seed=100 + i, phase=0.37 * i)
+        # constant-position prediction: start from the previous estimate, inflate P
+        gP, oP = gP + Q * 100, oP + Q * 100
+        gb, ob = g.fov_segment(gs[:3]), o.fov_segment(os_[:3])
+        assert np.array_equal(gb, ob)
+        g.scan_upload(scan)
+        o.scan_upload(scan)
+        gs, gP, _ = g.iekf_update(gs, gP)
+        os_, oP, _ = o.iekf_update(os_, oP)
+        ga = g.map_incremental(gs, True)
+        oa = o.map_incremental(os_, True)
+        assert ga == oa
+        traj_g.append(gs[:3].copy())
+        traj_o.append(os_[:3].copy())
+        assert np.abs(gs - os_).max() < STATE_TOL
+        if i % 4 == 0 or i == len(poses) - 1:
+            gx, gi = g.map_export()
+            ox, oi = o.map_export()
+            assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
+    ate = np.sqrt(np.mean(np.sum((np.array(traj_g) - np.array(traj_o)) ** 2, 1)))
+    assert ate < 1e-3
+    truth = np.array([t for _, t in poses[1:]])
+    assert np.sqrt(np.mean(np.sum((np.array(traj_g) - truth) ** 2, 1))) < 0.05
+    g.close()
+
+
+def test_edge_cases_and_errors(pkg, synth, small_world):
+    g = pkg.LioContext(0.5, max_points=4096, max_scan=256)
+    st = small_world["truth"]
+    with pytest.raises(pkg.LioError):  # no scan yet
+        g.h_share(st)
+    g.scan_upload(small_world["scan"][:100])
+    with pytest.raises(pkg.LioError):  # cached neighbours requested before any search
+        g.h_share(st, redo_knn=False)
+    H, z, n_eff, res = g.h_share(st, True)  # empty map: valid == false, all-zero normal equations
+    assert n_eff == 0 and not H.any() and not z.any() and res == 0
+    s2, P2, info = g.iekf_update(st, synth.default_cov(), trace=True)
+    assert np.array_equal(s2, st) and info["iters"] == 4 and (info["n_eff"] == 0).all()
+    with pytest.raises(pkg.LioError):  # scan larger than max_scan
+        g.scan_upload(small_world["scan"][:1000])
+    ids, d2, pts, cnt = g.map_knn(np.zeros((3, 3), np.float32), 5, 5.0)
+    assert (cnt == 0).all() and (ids == 0xFFFFFFFF).all() and np.isinf(d2).all()
+    with pytest.raises(pkg.LioError):
+        g.map_knn(np.zeros((3, 3), np.float32), 6, 5.0)
+    assert g.map_add(np.zeros((0, 3), np.float32)) == 0
+    # capacity exhaustion is reported, not silently dropped
+    with pytest.raises(pkg.LioError):
+        g.map_build(np.random.default_rng(0).uniform(-500, 500, (20000, 3)).astype(np.float32))
+    g.close()
+    with pytest.raises(pkg.LioError):
+        pkg.LioContext(0.5, max_points=0, max_scan=16)
+
+
+def test_full_size_properties(pkg, synth):
+    """BASELINE config-2 sizes (131,072-point scan, 2M-point map): size-independent properties instead of the oracle:
+    kNN on a sample vs brute force, H^T H symmetric PSD and equal to the row products, determinism, idempotence."""
+    rng = np.random.default_rng(11)
+    M, N = 2_000_000, 131_072
+    # planar-ish synthetic map: ground + two walls, one point per 0.5 m cell, jittered
+    gx, gy = np.meshgrid(np.arange(-500, 500, 0.5), np.arange(-400, 400, 0.5), indexing="ij")
+    ground = np.stack([gx.ravel(), gy.ravel(), np.zeros(gx.size)], 1)
+    wy, wz = np.meshgrid(np.arange(-400, 400, 0.5), np.arange(0, 62.5, 0.5), indexing="ij")
+    wall = np.stack([np.full(wy.size, 30.0), wy.ravel(), wz.ravel()], 1)
+    m = np.concatenate([ground, wall, wall * [-1, 1, 1]])[:M]
+    m = (m + rng.uniform(-0.2, 0.2, m.shape) * [1, 1, 0.05]).astype(np.float32)
+    assert len(m) == M
+    g = pkg.LioContext(0.5, max_points=M + (1 << 18), max_scan=N)
+    g.map_build(m)
+    assert g.map_size() == M
+    az = rng.uniform(0, 2 * np.pi, N)
+    r = rng.uniform(2, 100, N)
+    scan = np.stack([r * np.cos(az), r * np.sin(az), np.full(N, -1.8)], 1)
+    hit_wall = np.abs(scan[:, 0]) > 30
+    scan[hit_wall, 0] = np.sign(scan[hit_wall, 0]) * 30
+    scan[hit_wall, 2] = rng.uniform(-1.8, 40, hit_wall.sum())
+    scan = (scan + rng.normal(0, 0.02, scan.shape)).astype(np.float32)
+    st = synth.make_state(np.eye(3), [0, 0, 1.8])
+    g.scan_upload(scan)
+    H1, z1, n1, r1 = g.h_share(st, True)
+    H2, z2, n2, r2 = g.h_share(st, True)
+    assert n1 == n2 > 0.8 * N and np.array_equal(H1, H2) and np.array_equal(z1, z2)  # deterministic reduction
+    assert np.array_equal(H1, H1.T) and np.linalg.eigvalsh(H1[:6, :6]).min() > 0
+    sel, rows, z, n3 = g.h_share_rows(st, False)
+    assert n3 == n1
+    assert np.allclose(rows.T @ rows, H1, rtol=1e-9) and np.allclose(rows.T @ z, z1, rtol=1e-9, atol=1e-9)
+    out = g.scan_get()
+    idx = rng.integers(0, N, 64)
+    for i in idx:
+        d = m - out["world"][i]
+        d2 = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+        order = np.lexsort((np.arange(M), d2))[:5]
+        order = order[d2[order] <= 5.0]
+        assert out["nn_cnt"][i] == len(order)
+        assert np.array_equal(out["nn_ids"][i, : len(order)], order.astype(np.uint32))
+    # sortedness of every neighbour row
+    ids, d2, _, cnt = g.map_knn(out["world"][:20000], 5, 5.0)
+    assert (np.diff(d2, axis=1) >= 0).all()
+    assert np.array_equal(ids, out["nn_ids"][:20000])
+    # map_incremental twice: the second replay adds nothing that survives (idempotence of downsample-on-insert)
+    g.map_incremental(st, True)
+    s1 = g.map_size()
+    g.h_share(st, True)
+    a, b = g.map_incremental(st, True)
+    assert g.map_size() - s1 <= b  # only no-downsample points may accumulate
+    g.close()
