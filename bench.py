@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""Headline benchmark: IEKF scans/s on Ouster OS1-128-shaped scans (131,072 pts) against a 2M-point map
+(BASELINE.json configs[1]), and `--workload loop` for the batched loop-closure ICP (configs[3]).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload iekf|loop]
+
+One "step" = one scan through the hot path: esekfom's update_iterated_dyn_share_modified (up to
+max_iteration+1 = 4 calls of the GPU h_share_model: body->world, exact k=5 NN, plane fit, residual,
+Jacobian, FP64 H^T H / H^T z) followed by map_incremental (classification + downsample-on-insert).
+`value` times it with the scan already resident in HBM; `e2e` times the same call sequence through the
+C-ABI with HOST (pinned) scan buffers, the H2D copy and the D2H read of H^T H / H^T z inside the region.
+N > 1: the IEKF does not shard (iterations are sequential) -> replicas only, one independent sequence per
+GPU, no collective; scaling is weak.
+`--impl reference` times the CPU oracle (oracle/, the restatement of the reference's OpenMP path; the
+reference itself cannot be built here) on the host cores on the same workload.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_SCAN = 131072  # 128 x 1024
+N_MAP = 2_000_000
+ALGO_BYTES_PER_POINT = 96  # 16 B body point + 5 x 16 B neighbours, per query point per call
+MAX_ITER = 3
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="iekf", choices=["iekf", "loop"])
+    ap.add_argument("--scans", type=int, default=4, help="distinct synthetic scans cycled through")
+    ap.add_argument("--n-scan", type=int, default=N_SCAN)
+    ap.add_argument("--n-map", type=int, default=N_MAP)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# ------------------------------------------------------------------------------------------- workload
+def make_iekf_workload(synth, n_scan, n_map, n_scans, rank=0):
+    """Seeded street scene big enough for an n_map-point map at one point per 0.5 m cell; OS1-128 scans."""
+    half = 60.0
+    while True:
+        scene = synth.make_scene(half_extent=half, seed=synth.SEED + 1000 * rank)
+        # surface area estimate: ground + roofs ~ (2*half)^2, walls ~ 4 * w * h per block
+        nb = len(scene["boxes"])
+        est = ((2 * half) ** 2 + nb * 4 * 8.0 * 14.0) / 0.25
+        if est >= n_map * 1.05 or half > 600:
+            break
+        half += 20.0
+    m = synth.sample_map(scene, spacing=0.5, seed=synth.SEED + 1 + 1000 * rank)
+    while len(m) < n_map:  # rare: top up with a second, offset sampling
+        extra = synth.sample_map(scene, spacing=0.5, seed=synth.SEED + 7 + len(m))
+        m = np.concatenate([m, extra[: n_map - len(m)]])
+    m = np.ascontiguousarray(m[:n_map])
+    scans, truths, starts = [], [], []
+    for i in range(n_scans):
+        R = synth.rot_from_rpy(0.01 * i, -0.01, 0.2 + 0.3 * i)
+        t = np.array([-0.25 * half + 3.0 * i, 0.4 * i, 1.9])
+        s = synth.make_scan(scene, R, t, kind="os1_128", n_points=n_scan, seed=synth.SEED + 50 + i, max_range=min(120.0, half))
+        if len(s) < n_scan:  # sky-heavy pose: repeat returns with fresh noise so the scan has exactly n_scan points
+            rng = np.random.default_rng(i)
+            idx = rng.integers(0, len(s), n_scan - len(s))
+            s = np.concatenate([s, s[idx] + rng.normal(0, 0.01, (len(idx), 3)).astype(np.float32)])
+        scans.append(np.ascontiguousarray(s[:n_scan]))
+        st = synth.make_state(R, t)
+        truths.append(st)
+        starts.append(synth.perturb_state(st, seed=synth.SEED + 90 + i))
+    return dict(scene=scene, map=m, scans=scans, truths=truths, starts=starts, half=half)
+
+
+# ------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[j] for r in self.rows if len(r) >= 6 for j in range(4) if r[2 + j].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------- CPU legs
+def cpu_iekf(orc, synth, w, steps, warmup, with_map_update=True):
+    """The oracle (CPU restatement of the reference's OpenMP h_share_model + ikd-Tree + esekfom) on the same scans."""
+    cores = orc.max_threads()
+    o = orc.OracleLio(0.5, nthreads=cores)
+    o.map_build(w["map"])
+    P0 = synth.default_cov()
+    calls = 0
+    n_eff = 0
+    for i in range(warmup + steps):
+        if i == warmup:
+            t0 = time.perf_counter()
+            calls = n_eff = 0
+        j = i % len(w["scans"])
+        o.scan_upload(w["scans"][j])
+        s, P, info = o.iekf_update(w["starts"][j], P0, max_iter=MAX_ITER, trace=True)
+        calls += info["iters"]
+        n_eff += int(info["n_eff"].sum())
+        if with_map_update:
+            o.map_incremental(s, True)
+    dt = time.perf_counter() - t0
+    o.close()
+    return dict(scans_per_s=steps / dt, ms_per_step=1e3 * dt / steps, cores=cores, calls_per_scan=calls / steps, corr_per_s=n_eff / dt)
+
+
+def run_reference(args, synth):
+    from oracle import orc
+
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    orc.build()
+    w = make_iekf_workload(synth, args.n_scan, args.n_map, args.scans)
+    r = cpu_iekf(orc, synth, w, args.steps, max(1, min(args.warmup, 2)))
+    line = {
+        "impl": "reference", "metric": "IEKF scans/s", "value": r["scans_per_s"], "unit": "scans/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32 search/plane + f64 Jacobian/reduction", "data": "synthetic",
+        "config": workload_config(args, w, r["calls_per_scan"]),
+        "cpu_baseline": {"value": r["scans_per_s"], "unit": "scans/s", "cores": r["cores"], "kind": "port",
+                         "sample": f"{args.steps} full scans ({args.n_scan} pts x {r['calls_per_scan']:.2f} model calls + map_incremental) "
+                                   f"on the {args.n_map}-pt map; reference source absent -> oracle port, OpenMP over all host cores"},
+        "e2e": {"value": r["scans_per_s"], "unit": "scans/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "corr_per_s": r["corr_per_s"], "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, w, calls):
+    return {"workload": "configs[1]: OS1-128-shaped synthetic scans, IEKF h_share_model + map_incremental against a 2M-point map",
+            "points_per_scan": args.n_scan, "map_points": args.n_map, "k": 5, "max_iteration": MAX_ITER,
+            "model_calls_per_scan": round(float(calls), 3), "filter_size_map": 0.5, "distinct_scans": len(w["scans"]),
+            "state_perturbation": "5 cm / 0.5 deg", "l2_policy": "map (table+buckets > 126 MB L2 not guaranteed: see DESIGN.md); "
+            "a 256 MB buffer is written between timed steps to flush L2", "parallelism": "replicas (one sequence per GPU)"}
+
+
+# ------------------------------------------------------------------------------------------- GPU leg
+def run_ours(args, synth):
+    import torch
+    import torch.distributed as dist
+
+    pkg = importlib.import_module("fast-lio-sam_gps_b200")
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if not os.path.exists(pkg.LIB_PATH):
+        pkg.build_library()
+
+    w = make_iekf_workload(synth, args.n_scan, args.n_map, args.scans, rank=rank)
+    stream = torch.cuda.Stream()
+    g = pkg.LioContext(0.5, max_points=args.n_map + 8 * args.n_scan, max_scan=args.n_scan, device=local_rank, stream=stream.cuda_stream)
+    g.map_build(w["map"])
+    P0 = synth.default_cov()
+    ns = len(w["scans"])
+    # device-resident scans (float4) for the `value` leg, pinned host copies (xyz) for the `e2e` leg
+    dev_scans, pin_scans = [], []
+    for s in w["scans"]:
+        s4 = np.concatenate([s, np.zeros((len(s), 1), np.float32)], 1)
+        dev_scans.append(torch.from_numpy(s4).cuda())
+        pin_scans.append(torch.from_numpy(s.copy()).pin_memory())
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(i, host):
+        j = i % ns
+        if host:
+            g.scan_upload_ptr(pin_scans[j].data_ptr(), args.n_scan)
+        else:
+            g.scan_set_device(dev_scans[j].data_ptr(), args.n_scan)
+        s, P, info = g.iekf_update(w["starts"][j], P0, max_iter=MAX_ITER, trace=True)
+        g.map_incremental(s, True, want_counts=False)
+        return info
+
+    def timed(host, steps, warmup, sample_clocks):
+        for i in range(warmup):
+            step(i, host)
+        g.sync()
+        g.timing(True)
+        g.timing_reset()
+        l0 = g.launch_count()
+        evs = []
+        calls = n_eff = 0
+        clk = ClockSampler(local_rank) if sample_clocks else None
+        barrier()
+        for i in range(steps):
+            with torch.cuda.stream(stream):
+                flush.fill_(i & 255)  # L2 flush between timed steps (outside the event pair)
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream)
+                info = step(warmup + i, host)
+                b.record(stream)
+            evs.append((a, b))
+            calls += info["iters"]
+            n_eff += int(info["n_eff"].sum())
+        g.sync()
+        barrier()
+        clocks = clk.stop() if clk else None
+        total_ms = sum(a.elapsed_time(b) for a, b in evs)
+        launches = g.launch_count() - l0
+        kt = {k: g.timing_get(k) for k in ("knn", "plane_reduce", "insert", "classify")}
+        g.timing(False)
+        return total_ms, calls, n_eff, launches, kt, clocks
+
+    dev_ms, calls, n_eff, launches, kt, clocks = timed(False, args.steps, args.warmup, True)
+    e2e_ms, e_calls, _, _, _, _ = timed(True, args.steps, max(3, args.warmup), False)
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)  # max over ranks of the device-timed totals
+    dev_ms, e2e_ms = t.tolist()
+    total_scans = args.steps * world
+    value = total_scans / (dev_ms * 1e-3)
+    e2e = total_scans / (e2e_ms * 1e-3)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        knn_ms, knn_n = kt["knn"]
+        algo_bytes = ALGO_BYTES_PER_POINT * args.n_scan
+        achieved = algo_bytes / (knn_ms * 1e-3) / 1e9 if knn_ms > 0 else 0.0
+        line = {
+            "metric": "IEKF scans/s", "value": value, "unit": "scans/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 search/plane + f64 Jacobian/reduction", "data": "synthetic",
+            "config": workload_config(args, w, calls / args.steps),
+            "corr_per_s": n_eff * world / (dev_ms * 1e-3),
+            "e2e": {"value": e2e, "unit": "scans/s", "h2d_bytes_per_step": args.n_scan * 12 + 36 * 8,
+                    "d2h_bytes_per_step": int(round(e_calls / args.steps * 160 * 8))},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_scan_knn (body->world + exact k=5 NN)", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": knn_ms, "launches_timed": knn_n,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650"},
+            "kernel_ms": {k: {"mean_ms": v[0], "launches": v[1]} for k, v in kt.items()},
+            "clocks": clocks,
+        }
+        if not args.no_cpu_baseline and world == 1:
+            from oracle import orc
+
+            orc.build()
+            r = cpu_iekf(orc, synth, w, steps=max(2, min(6, args.steps)), warmup=1)
+            line["cpu_baseline"] = {"value": r["scans_per_s"], "unit": "scans/s", "cores": r["cores"], "kind": "port",
+                                    "sample": f"{max(2, min(6, args.steps))} full scans of the same workload (oracle port, OpenMP, all host cores)",
+                                    "ms_per_step": r["ms_per_step"]}
+        print(json.dumps(line))
+    g.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    synth = importlib.import_module("fast-lio-sam_gps_b200.synth")
+    if args.workload == "loop":
+        loop_bench = importlib.import_module("fast-lio-sam_gps_b200.loop_bench")
+        return loop_bench.main(args)
+    if args.impl == "reference":
+        return run_reference(args, synth)
+    return run_ours(args, synth)
+
+
+if __name__ == "__main__":
+    main()
