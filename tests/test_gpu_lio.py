@@ -198,46 +198,55 @@ def test_map_delete_boxes_parity(pkg, orc):
 
 def test_sequence_with_map_growth_ate(pkg, orc, synth):
     """Config-1/3 shaped slice: scans along a street, IEKF update + map_incremental every scan, local-map cube moving.
-    GPU and oracle run independently; live map sets must stay equal and the trajectories within 1 mm."""
+    Two GPU contexts against one oracle:
+      lock-step  - starts every scan from the ORACLE's state and inserts at the oracle's final state, so its inputs are
+                   identical to the oracle's: per-iteration states within 1e-6 and the live map bit-identical;
+      free-running - feeds its own estimates forward (its states differ from the oracle's by ~1e-15, which may flip the f32
+                   rounding of an inserted world point): trajectory divergence must stay under 1 mm."""
     scene = synth.make_scene(half_extent=60.0)
     poses = synth.street_poses(12, scene, step=0.7)
-    g = pkg.LioContext(0.5, max_points=1 << 19, max_scan=1 << 16, cube_side_length=100.0, det_range=20.0)
+    kw = dict(max_points=1 << 19, max_scan=1 << 16, cube_side_length=100.0, det_range=20.0)
+    g, f = pkg.LioContext(0.5, **kw), pkg.LioContext(0.5, **kw)
     o = orc.OracleLio(0.5, nthreads=0, cube_side_length=100.0, det_range=20.0)
     R0, t0 = poses[0]
     first = synth.make_scan(scene, R0, t0, kind="vlp16", seed=100)
     world0 = (first.astype(np.float64) @ R0.T + t0).astype(np.float32)
-    g.map_build(world0)
-    o.map_build(world0)
-    gs = os_ = synth.make_state(R0, t0)
-    gP = oP = synth.default_cov()
-    Q = np.eye(23) * 1e-5
-    traj_g, traj_o = [], []
+    for c in (g, f, o):
+        c.map_build(world0)
+    fs = os_ = synth.make_state(R0, t0)
+    fP = oP = synth.default_cov()
+    Q = np.eye(23) * 1e-3
+    traj_f, traj_o = [], []
     for i, (R, t) in enumerate(poses[1:], 1):
         kind = "avia" if i % 2 else "vlp16"
         scan = synth.make_scan(scene, R, t, kind=kind, seed=100 + i, phase=0.37 * i)
-        # constant-position prediction: start from the previous estimate, inflate P
-        gP, oP = gP + Q * 100, oP + Q * 100
-        gb, ob = g.fov_segment(gs[:3]), o.fov_segment(os_[:3])
-        assert np.array_equal(gb, ob)
-        g.scan_upload(scan)
-        o.scan_upload(scan)
-        gs, gP, _ = g.iekf_update(gs, gP)
-        os_, oP, _ = o.iekf_update(os_, oP)
-        ga = g.map_incremental(gs, True)
-        oa = o.map_incremental(os_, True)
-        assert ga == oa
-        traj_g.append(gs[:3].copy())
+        fP, oP = fP + Q, oP + Q  # constant-position prediction: start from the previous estimate, inflate P
+        ob = o.fov_segment(os_[:3])
+        assert np.array_equal(g.fov_segment(os_[:3]), ob)
+        f.fov_segment(fs[:3])
+        for c in (g, f, o):
+            c.scan_upload(scan)
+        gs, gP, gi = g.iekf_update(os_, oP, trace=True)
+        fs, fP, _ = f.iekf_update(fs, fP)
+        os_, oP, oi = o.iekf_update(os_, oP, trace=True)
+        assert gi["iters"] == oi["iters"] and np.array_equal(gi["n_eff"], oi["n_eff"])
+        assert np.abs(gi["states"] - oi["states"]).max() < STATE_TOL
+        assert np.abs(gs - os_).max() < STATE_TOL and np.abs(fs - os_).max() < 1e-4
+        assert g.map_incremental(os_, True) == o.map_incremental(os_, True)
+        f.map_incremental(fs, True)
+        traj_f.append(fs[:3].copy())
         traj_o.append(os_[:3].copy())
-        assert np.abs(gs - os_).max() < STATE_TOL
         if i % 4 == 0 or i == len(poses) - 1:
-            gx, gi = g.map_export()
-            ox, oi = o.map_export()
-            assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
-    ate = np.sqrt(np.mean(np.sum((np.array(traj_g) - np.array(traj_o)) ** 2, 1)))
+            gx, gid = g.map_export()
+            ox, oid = o.map_export()
+            assert np.array_equal(gid, oid) and np.array_equal(gx, ox)
+            assert abs(f.map_size() - o.map_size()) <= 0.001 * o.map_size()
+    ate = np.sqrt(np.mean(np.sum((np.array(traj_f) - np.array(traj_o)) ** 2, 1)))
     assert ate < 1e-3
     truth = np.array([t for _, t in poses[1:]])
-    assert np.sqrt(np.mean(np.sum((np.array(traj_g) - truth) ** 2, 1))) < 0.05
+    assert np.sqrt(np.mean(np.sum((np.array(traj_f) - truth) ** 2, 1))) < 0.05
     g.close()
+    f.close()
 
 
 def test_edge_cases_and_errors(pkg, synth, small_world):
