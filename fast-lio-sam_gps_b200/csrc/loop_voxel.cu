@@ -1,0 +1,398 @@
+// Submap accumulation + VoxelGrid downsample — kernels K6 of SURVEY.md §2.2.
+// Reference: LoopClosure::setSrcAndDstCloud (fast_lio_sam/src/loop_closure.cpp:42-67), transformPcd / voxelizePcd
+// (fast_lio_sam/include/utilities.hpp:132-171); pcl::VoxelGrid::applyFilter and pcl::transformPointCloud semantics per
+// SURVEY.md §9.5 (PCL 1.10 is not in the reference mount).
+//
+// All clouds ("jobs") of a batch are processed together:
+//   k_submap    : every raw point = pose_corrected * keyframe point (f64 math, f32 store), written at its place in the
+//                 concatenated cloud of its job; per-job bounding box and finite-point count by warp-aggregated atomics;
+//   k_grid      : per job, PCL's min/max box indices, the division multipliers and its index-overflow guard;
+//   k_keys      : 64-bit sort key (job << 32 | linear voxel index), value = raw index;
+//   radix sort  : one stable device-wide sort for the whole batch (cub::DeviceRadixSort — the only library call on this path);
+//   k_heads/scan: voxel heads -> output slots; k_centroids: one thread per voxel sums its points in ORIGINAL cloud order
+//                 in f32 (the order the oracle defines as canonical) and divides by the count.
+#include <algorithm>
+#include <cstring>
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include "loop_ctx.h"
+
+namespace loopb {
+
+namespace {
+
+__device__ __forceinline__ uint32_t f2ord(float f) {
+  const uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ord2f(uint32_t u) {
+  const uint32_t b = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  float f;
+  memcpy(&f, &b, 4);
+  return f;
+#endif
+}
+
+// per-job reduction cells: 6 ordered-uint box bounds + finite count
+struct BoxAcc {
+  uint32_t lo[3], hi[3], n_finite, pad;
+};
+
+__global__ void k_box_init(BoxAcc* acc, int n_jobs) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_jobs) return;
+  for (int a = 0; a < 3; ++a) {
+    acc[j].lo[a] = 0xFFFFFFFFu;
+    acc[j].hi[a] = 0u;
+  }
+  acc[j].n_finite = 0;
+}
+
+__device__ __forceinline__ int find_seg(const SegDev* segs, int n_segs, uint32_t i) {
+  int lo = 0, hi = n_segs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (segs[mid].dst_off <= i) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ int find_job(const JobDev* jobs, int n_jobs, uint32_t i) {
+  int lo = 0, hi = n_jobs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (jobs[mid].raw_off <= i) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+// raw[i] = T_seg * kf_pts[...]; with segs == nullptr the raw cloud is already in place (host-supplied)
+__global__ void __launch_bounds__(256) k_submap(const SegDev* __restrict__ segs, int n_segs, const JobDev* __restrict__ jobs, int n_jobs,
+                                                const float4* __restrict__ kf_pts, float4* __restrict__ raw, uint32_t n_raw,
+                                                BoxAcc* __restrict__ acc) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  int job = -1;
+  float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+  bool finite = false;
+  if (i < n_raw) {
+    if (segs) {
+      const int s = find_seg(segs, n_segs, i);
+      const SegDev& sg = segs[s];
+      job = (int)sg.job;
+      const float4 p = __ldg(kf_pts + sg.src_off + (i - sg.dst_off));
+      const double x = p.x, y = p.y, z = p.z;
+      const double* T = sg.T;
+      o.x = (float)(((T[0] * x + T[1] * y) + T[2] * z) + T[3]);
+      o.y = (float)(((T[4] * x + T[5] * y) + T[6] * z) + T[7]);
+      o.z = (float)(((T[8] * x + T[9] * y) + T[10] * z) + T[11]);
+      o.w = p.w;
+      raw[i] = o;
+    } else {
+      job = find_job(jobs, n_jobs, i);
+      o = raw[i];
+    }
+    finite = isfinite(o.x) && isfinite(o.y) && isfinite(o.z);
+  }
+  // warp-aggregated box update when the whole warp works on one job
+  const unsigned full = 0xFFFFFFFFu;
+  const int job0 = __shfl_sync(full, job, 0);
+  const bool uniform = __all_sync(full, job == job0 || job < 0) && job0 >= 0;
+  if (uniform) {
+    uint32_t lo[3] = {finite ? f2ord(o.x) : 0xFFFFFFFFu, finite ? f2ord(o.y) : 0xFFFFFFFFu, finite ? f2ord(o.z) : 0xFFFFFFFFu};
+    uint32_t hi[3] = {finite ? f2ord(o.x) : 0u, finite ? f2ord(o.y) : 0u, finite ? f2ord(o.z) : 0u};
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        lo[a] = min(lo[a], __shfl_xor_sync(full, lo[a], off));
+        hi[a] = max(hi[a], __shfl_xor_sync(full, hi[a], off));
+      }
+    }
+    const unsigned nf = __popc(__ballot_sync(full, finite));
+    if ((threadIdx.x & 31) == 0 && nf) {
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        atomicMin(&acc[job0].lo[a], lo[a]);
+        atomicMax(&acc[job0].hi[a], hi[a]);
+      }
+      atomicAdd(&acc[job0].n_finite, nf);
+    }
+  } else if (finite && job >= 0) {
+    atomicMin(&acc[job].lo[0], f2ord(o.x));
+    atomicMin(&acc[job].lo[1], f2ord(o.y));
+    atomicMin(&acc[job].lo[2], f2ord(o.z));
+    atomicMax(&acc[job].hi[0], f2ord(o.x));
+    atomicMax(&acc[job].hi[1], f2ord(o.y));
+    atomicMax(&acc[job].hi[2], f2ord(o.z));
+    atomicAdd(&acc[job].n_finite, 1u);
+  }
+}
+
+// PCL VoxelGrid::applyFilter prologue, one thread for all jobs (n_jobs is small); also the sorted offsets
+__global__ void k_grid(const BoxAcc* __restrict__ acc, GridDev* __restrict__ grids, int n_jobs, float leaf) {
+  if (blockIdx.x || threadIdx.x) return;
+  const float inv = 1.0f / leaf;
+  uint32_t run = 0;
+  for (int j = 0; j < n_jobs; ++j) {
+    GridDev g;
+    g.n_finite = acc[j].n_finite;
+    g.sorted_off = run;
+    run += g.n_finite;
+    g.overflow = 0;
+    g.vox_off = g.vox_n = 0;
+    g.mul1 = g.mul2 = 0;
+    long long d[3] = {1, 1, 1};
+    for (int a = 0; a < 3; ++a) {
+      g.lo[a] = g.n_finite ? ord2f(acc[j].lo[a]) : 0.f;
+      g.hi[a] = g.n_finite ? ord2f(acc[j].hi[a]) : 0.f;
+      g.minb[a] = (int)floorf(g.lo[a] * inv);
+      const int maxb = (int)floorf(g.hi[a] * inv);
+      d[a] = (long long)maxb - g.minb[a] + 1;
+    }
+    if (d[0] * d[1] * d[2] > 2147483647LL) {
+      g.overflow = 1;
+    } else {
+      g.mul1 = (int)d[0];
+      g.mul2 = (int)(d[0] * d[1]);
+    }
+    grids[j] = g;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_keys(const float4* __restrict__ raw, uint32_t n_raw, const JobDev* __restrict__ jobs, int n_jobs,
+                                              const GridDev* __restrict__ grids, float leaf, uint32_t sentinel,
+                                              unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_raw) return;
+  const float4 p = raw[i];
+  const int j = find_job(jobs, n_jobs, i);
+  unsigned long long key;
+  if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) {
+    key = (unsigned long long)sentinel << 32;
+  } else {
+    const GridDev& g = grids[j];
+    uint32_t lin;
+    if (g.overflow) {
+      lin = i - jobs[j].raw_off;  // every point its own voxel, original order: the cloud passes through unfiltered
+    } else {
+      const float inv = 1.0f / leaf;
+      const int i0 = (int)(floorf(p.x * inv) - (float)g.minb[0]);
+      const int i1 = (int)(floorf(p.y * inv) - (float)g.minb[1]);
+      const int i2 = (int)(floorf(p.z * inv) - (float)g.minb[2]);
+      lin = (uint32_t)(i0 + i1 * g.mul1 + i2 * g.mul2);
+    }
+    key = ((unsigned long long)(uint32_t)j << 32) | lin;
+  }
+  keys[i] = key;
+  vals[i] = i;
+}
+
+__global__ void __launch_bounds__(256) k_heads(const unsigned long long* __restrict__ keys, uint32_t n, uint32_t sentinel,
+                                               uint32_t* __restrict__ flags) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long k = keys[i];
+  const bool live = (uint32_t)(k >> 32) != sentinel;
+  flags[i] = (live && (i == 0 || keys[i - 1] != k)) ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(256) k_centroids(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals,
+                                                   const uint32_t* __restrict__ flags, const uint32_t* __restrict__ slot, uint32_t n,
+                                                   const float4* __restrict__ raw, float4* __restrict__ vox) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !flags[i]) return;
+  const unsigned long long k = keys[i];
+  float sx = 0.f, sy = 0.f, sz = 0.f, si = 0.f;
+  uint32_t j = i;
+  do {
+    const float4 p = __ldg(raw + vals[j]);
+    sx = sx + p.x;
+    sy = sy + p.y;
+    sz = sz + p.z;
+    si = si + p.w;
+    ++j;
+  } while (j < n && keys[j] == k);
+  const float cnt = (float)(j - i);
+  vox[slot[i]] = make_float4(sx / cnt, sy / cnt, sz / cnt, si / cnt);
+}
+
+// output ranges of the jobs in the voxelised buffer
+__global__ void k_job_ranges(GridDev* __restrict__ grids, int n_jobs, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ slot,
+                             uint32_t n_raw) {
+  if (blockIdx.x || threadIdx.x) return;
+  uint32_t total_finite = 0;
+  for (int j = 0; j < n_jobs; ++j) total_finite += grids[j].n_finite;
+  const uint32_t total_vox = total_finite ? slot[total_finite - 1] + flags[total_finite - 1] : 0u;
+  for (int j = 0; j < n_jobs; ++j) {
+    GridDev& g = grids[j];
+    const uint32_t b = g.n_finite ? slot[g.sorted_off] : 0u;
+    const uint32_t e_pos = g.sorted_off + g.n_finite;
+    const uint32_t e = (g.n_finite == 0) ? b : (e_pos < total_finite ? slot[e_pos] : total_vox);
+    g.vox_off = g.n_finite ? b : (j ? grids[j - 1].vox_off + grids[j - 1].vox_n : 0u);
+    g.vox_n = e - b;
+  }
+}
+
+int grid_of(size_t n, int block) { return (int)std::max<size_t>(1, (n + block - 1) / block); }
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// shared tail: raw cloud(s) are in c->raw, c->jobs describes them; produces c->vox + c->grids_host
+static int voxelize_raw(loop_ctx* c, const std::vector<JobDev>& jd, const SegDev* segs_dev, int n_segs, float leaf) {
+  const int n_jobs = (int)jd.size();
+  const uint32_t n_raw = n_jobs ? jd.back().raw_off + jd.back().raw_n : 0;
+  c->n_jobs = n_jobs;
+  c->grids_host.assign(n_jobs, GridDev{});
+  if (n_jobs == 0) return LOOP_OK;
+  cudaStream_t s = c->stream;
+  int rc;
+  if ((rc = c->jobs.ensure(n_jobs))) return rc;
+  if ((rc = c->grids.ensure(n_jobs))) return rc;
+  LOOP_CUDA(cudaMemcpyAsync(c->jobs.p, jd.data(), sizeof(JobDev) * n_jobs, cudaMemcpyHostToDevice, s));
+  // BoxAcc cells live at the head of the cub scratch buffer for the duration of the box pass
+  DevBuf<unsigned char>& tmp = c->cub_tmp;
+  if ((rc = tmp.ensure(sizeof(BoxAcc) * (size_t)n_jobs))) return rc;
+  BoxAcc* acc = reinterpret_cast<BoxAcc*>(tmp.p);
+  k_box_init<<<grid_of(n_jobs, 128), 128, 0, s>>>(acc, n_jobs);
+  c->launches += 1;
+  if (n_raw) {
+    if ((rc = c->keys_a.ensure(n_raw)) || (rc = c->keys_b.ensure(n_raw)) || (rc = c->vals_a.ensure(n_raw)) ||
+        (rc = c->vals_b.ensure(n_raw)) || (rc = c->head_scan.ensure(n_raw)) || (rc = c->vox.ensure(n_raw)))
+      return rc;
+    tbegin(c, LT_SUBMAP);
+    k_submap<<<grid_of(n_raw, 256), 256, 0, s>>>(segs_dev, n_segs, c->jobs.p, n_jobs, c->kf_pts.p, c->raw.p, n_raw, acc);
+    tend(c);
+    c->launches += 1;
+  }
+  tbegin(c, LT_VOXEL);
+  k_grid<<<1, 32, 0, s>>>(acc, c->grids.p, n_jobs, leaf);
+  c->launches += 1;
+  if (n_raw) {
+    int bits = 1;
+    while ((1u << bits) - 1u < (uint32_t)n_jobs) ++bits;  // sentinel = 2^bits - 1 >= n_jobs
+    const uint32_t sentinel = (1u << bits) - 1u;
+    k_keys<<<grid_of(n_raw, 256), 256, 0, s>>>(c->raw.p, n_raw, c->jobs.p, n_jobs, c->grids.p, leaf, sentinel, c->keys_a.p, c->vals_a.p);
+    c->launches += 1;
+    size_t need = 0, need2 = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, need, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)n_raw, 0, 32 + bits, s);
+    cub::DeviceScan::ExclusiveSum(nullptr, need2, c->vals_a.p, c->head_scan.p, (int)n_raw, s);
+    need = std::max(need, need2);
+    // the BoxAcc cells were consumed by k_grid (stream order), so the scratch buffer may be reallocated now
+    if (need > tmp.cap) {
+      LOOP_CUDA(cudaStreamSynchronize(s));
+      if ((rc = tmp.ensure(need))) return rc;
+    }
+    size_t bytes = tmp.cap;
+    LOOP_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, bytes, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)n_raw, 0, 32 + bits, s));
+    k_heads<<<grid_of(n_raw, 256), 256, 0, s>>>(c->keys_b.p, n_raw, sentinel, c->vals_a.p);
+    bytes = tmp.cap;
+    LOOP_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, bytes, c->vals_a.p, c->head_scan.p, (int)n_raw, s));
+    k_centroids<<<grid_of(n_raw, 256), 256, 0, s>>>(c->keys_b.p, c->vals_b.p, c->vals_a.p, c->head_scan.p, n_raw, c->raw.p, c->vox.p);
+    k_job_ranges<<<1, 32, 0, s>>>(c->grids.p, n_jobs, c->vals_a.p, c->head_scan.p, n_raw);
+    c->launches += 8;  // keys/heads/centroids/ranges + the library sort and scan passes (counted as one each)
+  }
+  tend(c);
+  LOOP_CUDA(cudaGetLastError());
+  LOOP_CUDA(cudaMemcpyAsync(c->grids_host.data(), c->grids.p, sizeof(GridDev) * n_jobs, cudaMemcpyDeviceToHost, s));
+  LOOP_CUDA(cudaStreamSynchronize(s));
+  return LOOP_OK;
+}
+
+int voxelize_jobs(loop_ctx* c, const std::vector<JobHost>& jobs_host, float leaf) {
+  std::vector<JobDev> jd;
+  std::vector<SegDev> sd;
+  uint64_t off = 0;
+  for (size_t j = 0; j < jobs_host.size(); ++j) {
+    JobDev d;
+    d.raw_off = (uint32_t)off;
+    d.seg_off = (uint32_t)sd.size();
+    for (int k : jobs_host[j].kf) {
+      if (c->kf_n[k] == 0) continue;
+      SegDev s;
+      s.src_off = c->kf_off[k];
+      s.n = c->kf_n[k];
+      s.dst_off = (uint32_t)off;
+      s.job = (uint32_t)j;
+      std::memcpy(s.T, &c->kf_pose[16 * (size_t)k], sizeof(double) * 12);
+      sd.push_back(s);
+      off += s.n;
+    }
+    d.raw_n = (uint32_t)(off - d.raw_off);
+    d.seg_n = (uint32_t)sd.size() - d.seg_off;
+    jd.push_back(d);
+  }
+  if (off >= 0x7FFFFFFFull) {
+    lio::set_error("batch chunk holds %llu raw points (limit 2^31-1): use smaller chunks", (unsigned long long)off);
+    return LOOP_E_CAPACITY;
+  }
+  int rc;
+  if ((rc = c->raw.ensure((size_t)off))) return rc;
+  if (!sd.empty()) {
+    if ((rc = c->segs.ensure(sd.size()))) return rc;
+    LOOP_CUDA(cudaMemcpyAsync(c->segs.p, sd.data(), sizeof(SegDev) * sd.size(), cudaMemcpyHostToDevice, c->stream));
+  }
+  // sd must outlive the async copy: voxelize_raw ends with a stream synchronise
+  return voxelize_raw(c, jd, sd.empty() ? nullptr : c->segs.p, (int)sd.size(), leaf);
+}
+
+int voxelize_host_cloud(loop_ctx* c, const float* xyzi, int n, float leaf) {
+  std::vector<JobDev> jd(1);
+  jd[0] = JobDev{0u, (uint32_t)n, 0u, 0u};
+  int rc;
+  if ((rc = c->raw.ensure((size_t)std::max(n, 1)))) return rc;
+  if (n) LOOP_CUDA(cudaMemcpyAsync(c->raw.p, xyzi, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  return voxelize_raw(c, jd, nullptr, 0, leaf);
+}
+
+int transform_host_cloud(loop_ctx* c, const float* xyzi, int n, const double* T16, float* out) {
+  if (n == 0) return LOOP_OK;
+  int rc;
+  // stage the input behind the keyframe store's live range, transform into raw
+  if ((rc = c->kf_pts.ensure(c->kf_used + (size_t)n, c->stream, true))) return rc;
+  if ((rc = c->raw.ensure((size_t)n)) || (rc = c->segs.ensure(1)) || (rc = c->jobs.ensure(1)) || (rc = c->cub_tmp.ensure(sizeof(BoxAcc))))
+    return rc;
+  LOOP_CUDA(cudaMemcpyAsync(c->kf_pts.p + c->kf_used, xyzi, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  SegDev s;
+  s.src_off = (uint32_t)c->kf_used;
+  s.n = (uint32_t)n;
+  s.dst_off = 0;
+  s.job = 0;
+  std::memcpy(s.T, T16, sizeof(double) * 12);
+  JobDev j{0u, (uint32_t)n, 0u, 1u};
+  LOOP_CUDA(cudaMemcpyAsync(c->segs.p, &s, sizeof(s), cudaMemcpyHostToDevice, c->stream));
+  LOOP_CUDA(cudaMemcpyAsync(c->jobs.p, &j, sizeof(j), cudaMemcpyHostToDevice, c->stream));
+  BoxAcc* acc = reinterpret_cast<BoxAcc*>(c->cub_tmp.p);
+  k_box_init<<<1, 32, 0, c->stream>>>(acc, 1);
+  k_submap<<<grid_of(n, 256), 256, 0, c->stream>>>(c->segs.p, 1, c->jobs.p, 1, c->kf_pts.p, c->raw.p, (uint32_t)n, acc);
+  c->launches += 2;
+  LOOP_CUDA(cudaGetLastError());
+  LOOP_CUDA(cudaMemcpyAsync(out, c->raw.p, sizeof(float4) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  LOOP_CUDA(cudaStreamSynchronize(c->stream));
+  return LOOP_OK;
+}
+
+// explicit clouds become the "voxelised" jobs of the batch, untouched (loop_icp_align)
+int load_clouds(loop_ctx* c, const float* const* clouds, const int* ns, int n_clouds) {
+  size_t total = 0;
+  for (int i = 0; i < n_clouds; ++i) total += (size_t)ns[i];
+  int rc;
+  if ((rc = c->vox.ensure(std::max<size_t>(total, 1)))) return rc;
+  c->n_jobs = n_clouds;
+  c->grids_host.assign(n_clouds, GridDev{});
+  size_t off = 0;
+  for (int i = 0; i < n_clouds; ++i) {
+    GridDev& g = c->grids_host[i];
+    g.vox_off = (uint32_t)off;
+    g.vox_n = (uint32_t)ns[i];
+    if (ns[i]) LOOP_CUDA(cudaMemcpyAsync(c->vox.p + off, clouds[i], sizeof(float4) * (size_t)ns[i], cudaMemcpyHostToDevice, c->stream));
+    off += (size_t)ns[i];
+  }
+  LOOP_CUDA(cudaStreamSynchronize(c->stream));
+  return LOOP_OK;
+}
+
+}  // namespace loopb

@@ -282,7 +282,7 @@ def test_full_size_properties(pkg, synth):
     rng = np.random.default_rng(11)
     M, N = 2_000_000, 131_072
     # planar-ish synthetic map: ground + two walls, one point per 0.5 m cell, jittered
-    gx, gy = np.meshgrid(np.arange(-500, 500, 0.5), np.arange(-400, 400, 0.5), indexing="ij")
+    gx, gy = np.meshgrid(np.arange(-250, 250, 0.5), np.arange(-400, 400, 0.5), indexing="ij")
     ground = np.stack([gx.ravel(), gy.ravel(), np.zeros(gx.size)], 1)
     wy, wz = np.meshgrid(np.arange(-400, 400, 0.5), np.arange(0, 62.5, 0.5), indexing="ij")
     wall = np.stack([np.full(wy.size, 30.0), wy.ravel(), wz.ravel()], 1)
