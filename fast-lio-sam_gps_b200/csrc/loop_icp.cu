@@ -1,0 +1,771 @@
+// Batched point-to-point ICP verification — kernels K7 (exact 1-NN), K8 (fused reductions + closed-form solve) and
+// K9 (all pairs of a batch advanced together) of SURVEY.md §2.2.
+// Reference: LoopClosure::icpAlignment (fast_lio_sam/src/loop_closure.cpp:69-92, parameters :7-11); the PCL 1.10 pieces it
+// calls (IterativeClosestPoint::computeTransformation, CorrespondenceEstimation over KdTreeFLANN, TransformationEstimationSVD
+// = Eigen::umeyama without scaling, DefaultConvergenceCriteria, getFitnessScore) follow SURVEY.md §9.4; operation order is
+// that of oracle/orc_icp.cpp so that transforms, iteration counts and scores compare bit-for-bit.
+//
+// Target side: one implicit balanced tree per target cloud over Morton-sorted points; a leaf is 8 float4 = one 128-byte
+// line, a node holds the boxes of its two children (64 bytes).  Search is exact (box pruning with a relative slack, ties
+// -> smaller original index) and unbounded, as pcl's kd-tree search is; max_corr_dist is applied afterwards.
+// Reductions are exact 64-bit fixed-point sums (order independent), so the parallel result equals the serial oracle's.
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <cub/device/device_radix_sort.cuh>
+#include "loop_ctx.h"
+#include "loop_device.cuh"
+
+namespace loopb {
+
+namespace {
+
+constexpr int kBlock = 256;
+constexpr int kWarps = kBlock / 32;
+constexpr uint32_t kPadIdx = 0x7FFFFFFFu;
+
+int grid_of(size_t n, int block) { return (int)std::max<size_t>(1, (n + block - 1) / block); }
+
+// compact index space of all tree points: tree t owns [cmp_off[t], cmp_off[t] + n)
+__device__ __forceinline__ int find_tree(const uint32_t* __restrict__ cmp_off, int n_trees, uint32_t i) {
+  int lo = 0, hi = n_trees - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (cmp_off[mid] <= i) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+__global__ void k_tree_box_init(BoxAcc* acc, int n) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  for (int a = 0; a < 3; ++a) {
+    acc[j].lo[a] = 0xFFFFFFFFu;
+    acc[j].hi[a] = 0u;
+  }
+  acc[j].n_finite = 0;
+}
+
+__global__ void __launch_bounds__(kBlock) k_tree_box(const TreeDev* __restrict__ trees, const uint32_t* __restrict__ cmp_off, int n_trees,
+                                                     uint32_t n_total, const float4* __restrict__ vox, BoxAcc* __restrict__ acc) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_total) return;
+  const int t = find_tree(cmp_off, n_trees, i);
+  const float4 p = __ldg(vox + trees[t].src_off + (i - cmp_off[t]));
+  if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) return;
+  atomicMin(&acc[t].lo[0], f2ord(p.x));
+  atomicMin(&acc[t].lo[1], f2ord(p.y));
+  atomicMin(&acc[t].lo[2], f2ord(p.z));
+  atomicMax(&acc[t].hi[0], f2ord(p.x));
+  atomicMax(&acc[t].hi[1], f2ord(p.y));
+  atomicMax(&acc[t].hi[2], f2ord(p.z));
+}
+
+__device__ __forceinline__ uint32_t spread10(uint32_t v) {
+  v &= 0x3FFu;
+  v = (v | (v << 16)) & 0x030000FFu;
+  v = (v | (v << 8)) & 0x0300F00Fu;
+  v = (v | (v << 4)) & 0x030C30C3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+
+// sort key (tree << 32 | 30-bit Morton code inside the tree's box); only the ORDER matters, not exactness
+__global__ void __launch_bounds__(kBlock) k_tree_keys(const TreeDev* __restrict__ trees, const uint32_t* __restrict__ cmp_off, int n_trees,
+                                                      uint32_t n_total, const float4* __restrict__ vox, const BoxAcc* __restrict__ acc,
+                                                      unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_total) return;
+  const int t = find_tree(cmp_off, n_trees, i);
+  const uint32_t l = i - cmp_off[t];
+  const float4 p = __ldg(vox + trees[t].src_off + l);
+  uint32_t code = 0x3FFFFFFFu;  // non-finite points sort last inside their tree and are never matched
+  if (isfinite(p.x) && isfinite(p.y) && isfinite(p.z)) {
+    const float lo[3] = {ord2f(acc[t].lo[0]), ord2f(acc[t].lo[1]), ord2f(acc[t].lo[2])};
+    const float hi[3] = {ord2f(acc[t].hi[0]), ord2f(acc[t].hi[1]), ord2f(acc[t].hi[2])};
+    const float ext = fmaxf(fmaxf(hi[0] - lo[0], hi[1] - lo[1]), fmaxf(hi[2] - lo[2], 1e-6f));
+    const float sc = 1023.0f / ext;
+    const uint32_t qx = (uint32_t)fminf(fmaxf((p.x - lo[0]) * sc, 0.f), 1023.f);
+    const uint32_t qy = (uint32_t)fminf(fmaxf((p.y - lo[1]) * sc, 0.f), 1023.f);
+    const uint32_t qz = (uint32_t)fminf(fmaxf((p.z - lo[2]) * sc, 0.f), 1023.f);
+    code = spread10(qx) | (spread10(qy) << 1) | (spread10(qz) << 2);
+  }
+  keys[i] = ((unsigned long long)(uint32_t)t << 32) | code;
+  vals[i] = l;
+}
+
+// tree_pts[pts_off + r] = (xyz of the r-th point in Morton order, original index); leaves padded with +inf points
+__global__ void __launch_bounds__(kBlock) k_tree_gather(const TreeDev* __restrict__ trees, int n_trees, const uint32_t* __restrict__ cmp_off,
+                                                        const uint32_t* __restrict__ pad_off, uint32_t n_pad_total,
+                                                        const uint32_t* __restrict__ vals_sorted, const float4* __restrict__ vox,
+                                                        float4* __restrict__ tree_pts) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pad_total) return;
+  const int t = find_tree(pad_off, n_trees, i);
+  const TreeDev& tr = trees[t];
+  const uint32_t r = i - pad_off[t];
+  float4 o = make_float4(INFINITY, INFINITY, INFINITY, __uint_as_float(kPadIdx));
+  if (r < tr.n) {
+    const uint32_t l = vals_sorted[cmp_off[t] + r];
+    const float4 p = __ldg(vox + tr.src_off + l);
+    if (isfinite(p.x) && isfinite(p.y) && isfinite(p.z)) o = make_float4(p.x, p.y, p.z, __uint_as_float(l));
+  }
+  tree_pts[i] = o;
+}
+
+__device__ __forceinline__ void box_of_leaf(const float4* __restrict__ pts, uint32_t leaf, uint32_t nleaf, float4& lo, float4& hi) {
+  lo = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
+  hi = make_float4(-INFINITY, -INFINITY, -INFINITY, 0.f);
+  if (leaf >= nleaf) return;
+#pragma unroll
+  for (int k = 0; k < kLeafPts; ++k) {
+    const float4 p = pts[(size_t)leaf * kLeafPts + k];
+    if (__float_as_uint(p.w) == kPadIdx) continue;
+    lo.x = fminf(lo.x, p.x); lo.y = fminf(lo.y, p.y); lo.z = fminf(lo.z, p.z);
+    hi.x = fmaxf(hi.x, p.x); hi.y = fmaxf(hi.y, p.y); hi.z = fmaxf(hi.z, p.z);
+  }
+}
+
+// one block per tree: bottom level from the leaves, then level by level up to the root
+__global__ void __launch_bounds__(1024) k_tree_nodes(const TreeDev* __restrict__ trees, const float4* __restrict__ tree_pts,
+                                                     Node2* __restrict__ nodes) {
+  const TreeDev tr = trees[blockIdx.x];
+  Node2* nd = nodes + tr.node_off;
+  const float4* pts = tree_pts + tr.pts_off;
+  const uint32_t half = tr.nleaf_pad >> 1;
+  for (uint32_t i = half + threadIdx.x; i < tr.nleaf_pad; i += blockDim.x) {
+    Node2 n;
+    box_of_leaf(pts, 2 * i - tr.nleaf_pad, tr.nleaf, n.lo0, n.hi0);
+    box_of_leaf(pts, 2 * i + 1 - tr.nleaf_pad, tr.nleaf, n.lo1, n.hi1);
+    nd[i] = n;
+  }
+  for (uint32_t lvl = half >> 1; lvl >= 1; lvl >>= 1) {
+    __syncthreads();
+    for (uint32_t i = lvl + threadIdx.x; i < 2 * lvl; i += blockDim.x) {
+      const Node2 a = nd[2 * i], b = nd[2 * i + 1];
+      Node2 n;
+      n.lo0 = make_float4(fminf(a.lo0.x, a.lo1.x), fminf(a.lo0.y, a.lo1.y), fminf(a.lo0.z, a.lo1.z), 0.f);
+      n.hi0 = make_float4(fmaxf(a.hi0.x, a.hi1.x), fmaxf(a.hi0.y, a.hi1.y), fmaxf(a.hi0.z, a.hi1.z), 0.f);
+      n.lo1 = make_float4(fminf(b.lo0.x, b.lo1.x), fminf(b.lo0.y, b.lo1.y), fminf(b.lo0.z, b.lo1.z), 0.f);
+      n.hi1 = make_float4(fmaxf(b.hi0.x, b.hi1.x), fmaxf(b.hi0.y, b.hi1.y), fmaxf(b.hi0.z, b.hi1.z), 0.f);
+      nd[i] = n;
+    }
+    if (lvl == 1) break;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ exact 1-NN
+__device__ __forceinline__ float box_d2(float qx, float qy, float qz, const float4& lo, const float4& hi) {
+  float dx = 0.f, dy = 0.f, dz = 0.f;
+  if (qx < lo.x) dx = lo.x - qx; else if (qx > hi.x) dx = qx - hi.x;
+  if (qy < lo.y) dy = lo.y - qy; else if (qy > hi.y) dy = qy - hi.y;
+  if (qz < lo.z) dz = lo.z - qz; else if (qz > hi.z) dz = qz - hi.z;
+  return dx * dx + dy * dy + dz * dz;  // an empty box (lo = +inf) yields +inf
+}
+
+__device__ __forceinline__ void scan_leaf(const float4* __restrict__ pts, uint32_t leaf, float qx, float qy, float qz, float& bd,
+                                          uint32_t& bi, float4& bp) {
+  const float4* lp = pts + (size_t)leaf * kLeafPts;
+#pragma unroll
+  for (int k = 0; k < kLeafPts; ++k) {
+    const float4 p = __ldg(lp + k);
+    const uint32_t idx = __float_as_uint(p.w);
+    const float d2 = sqd3(qx, qy, qz, p.x, p.y, p.z);
+    if (idx != kPadIdx && (d2 < bd || (d2 == bd && idx < bi))) {
+      bd = d2;
+      bi = idx;
+      bp = p;
+    }
+  }
+}
+
+// a subtree is visited unless it is empty (box distance +inf) or provably farther than the best so far; the box bound is
+// rounded differently from point distances, hence the relative slack (more visits, never fewer: exactness is kept)
+__device__ __forceinline__ bool visit(float d, float bd) { return d < INFINITY && d * 0.9999f <= bd; }
+
+// Exact nearest neighbour of q in tree `tr`; bi = original index in the target cloud (kPadIdx: none), bp = its point.
+__device__ void nn_search(const TreeDev& tr, const Node2* __restrict__ nodes, const float4* __restrict__ tree_pts, float qx, float qy,
+                          float qz, float& bd, uint32_t& bi, float4& bp) {
+  bd = INFINITY;
+  bi = kPadIdx;
+  bp = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (tr.n == 0 || !(isfinite(qx) && isfinite(qy) && isfinite(qz))) return;
+  const Node2* nd = nodes + tr.node_off;
+  const float4* pts = tree_pts + tr.pts_off;
+  const uint32_t first_leaf_parent = tr.nleaf_pad >> 1;
+  uint32_t st_node[24];
+  float st_d[24];
+  int sp = 0;
+  uint32_t node = 1;
+  while (true) {
+    const Node2 n = nd[node];
+    float d0 = box_d2(qx, qy, qz, n.lo0, n.hi0), d1 = box_d2(qx, qy, qz, n.lo1, n.hi1);
+    uint32_t c0 = 2 * node, c1 = c0 + 1;
+    if (d1 < d0) {  // nearer child first
+      const float td = d0; d0 = d1; d1 = td;
+      const uint32_t tc = c0; c0 = c1; c1 = tc;
+    }
+    uint32_t next = 0;
+    if (node >= first_leaf_parent) {  // children are leaves
+      if (visit(d0, bd)) scan_leaf(pts, c0 - tr.nleaf_pad, qx, qy, qz, bd, bi, bp);
+      if (visit(d1, bd)) scan_leaf(pts, c1 - tr.nleaf_pad, qx, qy, qz, bd, bi, bp);
+    } else {
+      const bool v0 = visit(d0, bd), v1 = visit(d1, bd);
+      if (v0) {
+        next = c0;
+        if (v1) {
+          st_node[sp] = c1;
+          st_d[sp] = d1;
+          ++sp;
+        }
+      } else if (v1) {
+        next = c1;
+      }
+    }
+    while (!next && sp > 0) {
+      --sp;
+      if (visit(st_d[sp], bd)) next = st_node[sp];
+    }
+    if (!next) break;
+    node = next;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ ICP iteration
+__device__ __forceinline__ void tf_f(const float* T, float x, float y, float z, float& ox, float& oy, float& oz) {
+  ox = ((T[0] * x + T[1] * y) + T[2] * z) + T[3];
+  oy = ((T[4] * x + T[5] * y) + T[6] * z) + T[7];
+  oz = ((T[8] * x + T[9] * y) + T[10] * z) + T[11];
+}
+// pcl::transformPointCloud<PointT, float> SSE association used by getFitnessScore: p0 + (p1 + (p2 + c3))
+__device__ __forceinline__ void tf_f_sse(const float* T, float x, float y, float z, float& ox, float& oy, float& oz) {
+  ox = T[0] * x + (T[1] * y + (T[2] * z + T[3]));
+  oy = T[4] * x + (T[5] * y + (T[6] * z + T[7]));
+  oz = T[8] * x + (T[9] * y + (T[10] * z + T[11]));
+}
+
+// correspondence search + first-moment sums.  mode 0: ICP iteration, mode 1: fitness score pass.
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) k_icp_nn(PairDev* __restrict__ pairs, const uint32_t* __restrict__ blk2pair,
+                                                   const float4* __restrict__ vox, float4* __restrict__ cur, int* __restrict__ match,
+                                                   float* __restrict__ md2, const TreeDev* __restrict__ trees,
+                                                   const Node2* __restrict__ nodes, const float4* __restrict__ tree_pts, double max_d2) {
+  __shared__ long long s_red[kWarps][8];
+  __shared__ float s_T[16];
+  const uint32_t p = blk2pair[2 * blockIdx.x], first = blk2pair[2 * blockIdx.x + 1];
+  PairDev& pr = pairs[p];
+  if (MODE == 0 && !pr.active) return;
+  if (threadIdx.x < 16) s_T[threadIdx.x] = (MODE == 0) ? pr.Tr[threadIdx.x] : pr.Tfinal[threadIdx.x];
+  __syncthreads();
+  const uint32_t l = first + threadIdx.x;
+  long long v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (l < pr.src_n) {
+    const size_t ci = (size_t)pr.cur_off + l;
+    float x, y, z;
+    if (MODE == 0) {
+      if (pr.iters == 0) {
+        const float4 s = __ldg(vox + pr.src_off + l);
+        x = s.x; y = s.y; z = s.z;
+      } else {
+        const float4 c = cur[ci];
+        tf_f(s_T, c.x, c.y, c.z, x, y, z);
+      }
+      cur[ci] = make_float4(x, y, z, 0.f);
+    } else {
+      const float4 s = __ldg(vox + pr.src_off + l);
+      tf_f_sse(s_T, s.x, s.y, s.z, x, y, z);
+    }
+    float bd;
+    uint32_t bi;
+    float4 bp;
+    nn_search(trees[pr.dst_job], nodes, tree_pts, x, y, z, bd, bi, bp);
+    if (MODE == 0) {
+      const bool ok = bi != kPadIdx && !((double)bd > max_d2);
+      match[ci] = ok ? (int)bi : -1;
+      md2[ci] = bd;
+      if (ok) {
+        v[0] = fixc(x); v[1] = fixc(y); v[2] = fixc(z);
+        v[3] = fixc(bp.x); v[4] = fixc(bp.y); v[5] = fixc(bp.z);
+        v[6] = fixp((double)bd);
+        v[7] = 1;
+      }
+    } else if (bi != kPadIdx) {
+      v[6] = fixp((double)bd);
+      v[7] = 1;
+    }
+  }
+  const long long tot = block_sum_ll<8, kWarps>(v, s_red);
+  if (threadIdx.x < 8 && tot != 0) {
+    long long* dst;
+    if (MODE == 0) dst = (threadIdx.x < 3) ? &pr.ss[threadIdx.x] : (threadIdx.x < 6) ? &pr.sd[threadIdx.x - 3] : (threadIdx.x == 6) ? &pr.mse_fix : &pr.cnt;
+    else dst = (threadIdx.x == 6) ? &pr.score_fix : &pr.score_n;
+    if (MODE == 0 || threadIdx.x >= 6) atomic_add_ll(dst, tot);
+  }
+}
+
+// second-moment sums about the f32 means (Eigen::umeyama: src_demean / dst_demean, sigma = dst_demean * src_demean^T / n)
+__global__ void __launch_bounds__(kBlock) k_icp_cov(PairDev* __restrict__ pairs, const uint32_t* __restrict__ blk2pair,
+                                                    const float4* __restrict__ vox, const float4* __restrict__ cur,
+                                                    const int* __restrict__ match, const TreeDev* __restrict__ trees, int min_corr) {
+  __shared__ long long s_red[kWarps][9];
+  const uint32_t p = blk2pair[2 * blockIdx.x], first = blk2pair[2 * blockIdx.x + 1];
+  PairDev& pr = pairs[p];
+  if (!pr.active) return;
+  const long long n = pr.cnt;
+  if (n < min_corr) return;
+  float ms[3], md[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    ms[a] = (float)(((double)pr.ss[a] / kFixCoord) / (double)n);
+    md[a] = (float)(((double)pr.sd[a] / kFixCoord) / (double)n);
+  }
+  const uint32_t l = first + threadIdx.x;
+  long long v[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (l < pr.src_n) {
+    const size_t ci = (size_t)pr.cur_off + l;
+    const int m = match[ci];
+    if (m >= 0) {
+      const float4 c = cur[ci];
+      const float4 d = __ldg(vox + trees[pr.dst_job].src_off + m);
+      const float a[3] = {c.x - ms[0], c.y - ms[1], c.z - ms[2]};
+      const float b[3] = {d.x - md[0], d.y - md[1], d.z - md[2]};
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc) v[r * 3 + cc] = fixp((double)b[r] * (double)a[cc]);
+    }
+  }
+  const long long tot = block_sum_ll<9, kWarps>(v, s_red);
+  if (threadIdx.x < 9 && tot != 0) atomic_add_ll(&pr.cov[threadIdx.x], tot);
+}
+
+// ------------------------------------------------------------------------------------------------ closed-form solve
+// 3x3 two-sided Jacobi SVD in f32 with Eigen::JacobiSVD's structure; same operation order as oracle/orc_icp.cpp svd3().
+struct Rot {
+  float c, s;
+};
+__device__ __forceinline__ void rot_apply(float& x, float& y, Rot j) {
+  const float xn = j.c * x + j.s * y;
+  const float yn = j.c * y - j.s * x;
+  x = xn;
+  y = yn;
+}
+__device__ __forceinline__ void rot_left(float* W, int p, int q, Rot j) {
+  for (int k = 0; k < 3; ++k) rot_apply(W[p * 3 + k], W[q * 3 + k], j);
+}
+__device__ __forceinline__ void rot_right(float* W, int p, int q, Rot j) {
+  const Rot t = {j.c, -j.s};
+  for (int k = 0; k < 3; ++k) rot_apply(W[k * 3 + p], W[k * 3 + q], t);
+}
+__device__ __forceinline__ void make_jacobi(float x, float y, float z, Rot& j) {
+  const float deno = 2.0f * fabsf(y);
+  if (deno < FLT_MIN) {
+    j.c = 1.f;
+    j.s = 0.f;
+    return;
+  }
+  const float tau = (x - z) / deno;
+  const float w = sqrtf(tau * tau + 1.0f);
+  const float t = tau > 0.f ? 1.0f / (tau + w) : 1.0f / (tau - w);
+  const float sign_t = t > 0.f ? 1.0f : -1.0f;
+  const float n = 1.0f / sqrtf(t * t + 1.0f);
+  const float ysign = y > 0.f ? 1.0f : -1.0f;
+  j.s = -sign_t * ysign * fabsf(t) * n;
+  j.c = n;
+}
+
+__device__ void svd3(const float* M, float* U, float* S, float* V) {
+  float W[9];
+  float scale = 0.f;
+  for (int i = 0; i < 9; ++i) scale = fmaxf(scale, fabsf(M[i]));
+  if (!(scale > 0.f)) scale = 1.0f;
+  for (int i = 0; i < 9; ++i) {
+    W[i] = M[i] / scale;
+    U[i] = V[i] = (i % 4 == 0) ? 1.f : 0.f;
+  }
+  const float precision = 2.0f * FLT_EPSILON;
+  float maxdiag = fmaxf(fabsf(W[0]), fmaxf(fabsf(W[4]), fabsf(W[8])));
+  bool finished = false;
+  int sweeps = 0;
+  while (!finished && sweeps < 64) {
+    finished = true;
+    ++sweeps;
+    for (int p = 1; p < 3; ++p)
+      for (int q = 0; q < p; ++q) {
+        const float thr = fmaxf(FLT_MIN, precision * maxdiag);
+        if (fabsf(W[p * 3 + q]) > thr || fabsf(W[q * 3 + p]) > thr) {
+          finished = false;
+          float m00 = W[p * 3 + p], m01 = W[p * 3 + q], m10 = W[q * 3 + p], m11 = W[q * 3 + q];
+          const float t = m00 + m11, d = m10 - m01;
+          Rot r1;
+          if (fabsf(d) < FLT_MIN) {
+            r1.s = 0.f;
+            r1.c = 1.f;
+          } else {
+            const float u = t / d;
+            const float tmp = sqrtf(1.0f + u * u);
+            r1.s = 1.0f / tmp;
+            r1.c = u / tmp;
+          }
+          rot_apply(m00, m10, r1);
+          rot_apply(m01, m11, r1);
+          Rot jr;
+          make_jacobi(m00, m01, m11, jr);
+          const Rot jrt = {jr.c, -jr.s};
+          const Rot jl = {r1.c * jrt.c - r1.s * jrt.s, r1.c * jrt.s + r1.s * jrt.c};
+          rot_left(W, p, q, jl);
+          {
+            const Rot jlt = {jl.c, -jl.s};
+            rot_right(U, p, q, jlt);
+          }
+          rot_right(W, p, q, jr);
+          rot_right(V, p, q, jr);
+          maxdiag = fmaxf(maxdiag, fmaxf(fabsf(W[p * 3 + p]), fabsf(W[q * 3 + q])));
+        }
+      }
+  }
+  for (int i = 0; i < 3; ++i) {
+    const float a = W[i * 3 + i];
+    S[i] = fabsf(a);
+    if (a < 0.f)
+      for (int k = 0; k < 3; ++k) U[k * 3 + i] = -U[k * 3 + i];
+    S[i] = S[i] * scale;
+  }
+  for (int i = 0; i < 3; ++i) {
+    int b = i;
+    for (int k = i + 1; k < 3; ++k)
+      if (S[k] > S[b]) b = k;
+    if (b != i) {
+      float t = S[i]; S[i] = S[b]; S[b] = t;
+      for (int k = 0; k < 3; ++k) {
+        t = U[k * 3 + i]; U[k * 3 + i] = U[k * 3 + b]; U[k * 3 + b] = t;
+        t = V[k * 3 + i]; V[k * 3 + i] = V[k * 3 + b]; V[k * 3 + b] = t;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ float det3(const float* A) {
+  const float a = A[0] * (A[4] * A[8] - A[5] * A[7]);
+  const float b = A[1] * (A[3] * A[8] - A[5] * A[6]);
+  const float c = A[2] * (A[3] * A[7] - A[4] * A[6]);
+  return (a - b) + c;
+}
+
+// one thread per pair: umeyama from the sums, compose, DefaultConvergenceCriteria, reset the accumulators
+__global__ void k_icp_solve(PairDev* __restrict__ pairs, int n_pairs, IcpParams prm, int* __restrict__ n_active) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pairs) return;
+  PairDev& pr = pairs[p];
+  if (!pr.active) return;
+  const long long n = pr.cnt;
+  bool done = false;
+  if (n < prm.min_corr) {
+    pr.state = 5;
+    pr.converged = 0;
+    done = true;
+  } else {
+    float ms[3], md[3], sigma[9];
+    for (int a = 0; a < 3; ++a) {
+      ms[a] = (float)(((double)pr.ss[a] / kFixCoord) / (double)n);
+      md[a] = (float)(((double)pr.sd[a] / kFixCoord) / (double)n);
+    }
+    for (int k = 0; k < 9; ++k) sigma[k] = (float)(((double)pr.cov[k] / kFixProd) / (double)n);
+    float U[9], S[3], V[9], R[9], Tr[16];
+    svd3(sigma, U, S, V);
+    const float sgn = (det3(U) * det3(V) < 0.f) ? -1.0f : 1.0f;
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) {
+        const float v = U[r * 3 + 0] * V[c * 3 + 0] + U[r * 3 + 1] * V[c * 3 + 1];
+        R[r * 3 + c] = v + (U[r * 3 + 2] * sgn) * V[c * 3 + 2];
+      }
+    for (int r = 0; r < 3; ++r) {
+      const float rs = (R[r * 3 + 0] * ms[0] + R[r * 3 + 1] * ms[1]) + R[r * 3 + 2] * ms[2];
+      Tr[r * 4 + 0] = R[r * 3 + 0];
+      Tr[r * 4 + 1] = R[r * 3 + 1];
+      Tr[r * 4 + 2] = R[r * 3 + 2];
+      Tr[r * 4 + 3] = md[r] - rs;
+    }
+    Tr[12] = Tr[13] = Tr[14] = 0.f;
+    Tr[15] = 1.f;
+    // final_transformation_ = transformation_ * final_transformation_
+    float Tf[16];
+    for (int r = 0; r < 4; ++r)
+      for (int c = 0; c < 4; ++c) {
+        float s = Tr[r * 4 + 0] * pr.Tfinal[0 * 4 + c] + Tr[r * 4 + 1] * pr.Tfinal[1 * 4 + c];
+        s = s + Tr[r * 4 + 2] * pr.Tfinal[2 * 4 + c];
+        Tf[r * 4 + c] = s + Tr[r * 4 + 3] * pr.Tfinal[3 * 4 + c];
+      }
+    for (int k = 0; k < 16; ++k) {
+      pr.Tr[k] = Tr[k];
+      pr.Tfinal[k] = Tf[k];
+    }
+    pr.iters += 1;
+    // DefaultConvergenceCriteria::hasConverged
+    if (pr.iters >= prm.max_iter) {
+      pr.state = 1;
+      pr.converged = 1;
+      done = true;
+    } else {
+      bool is_similar = false;
+      const double cos_angle = 0.5 * (((double)Tr[0] + (double)Tr[5] + (double)Tr[10]) - 1.0);
+      const double tr2 = ((double)Tr[3] * (double)Tr[3] + (double)Tr[7] * (double)Tr[7]) + (double)Tr[11] * (double)Tr[11];
+      if (cos_angle >= prm.rot_thr && tr2 <= prm.trans_eps) {
+        if (pr.similar >= prm.max_similar) {
+          pr.state = 2;
+          pr.converged = 1;
+          done = true;
+        }
+        is_similar = true;
+      }
+      const double mse = ((double)pr.mse_fix / kFixProd) / (double)n;
+      if (!done && fabs(mse - pr.prev_mse) < prm.mse_abs) {
+        if (pr.similar >= prm.max_similar) {
+          pr.state = 3;
+          pr.converged = 1;
+          done = true;
+        }
+        is_similar = true;
+      }
+      if (!done && fabs(mse - pr.prev_mse) / pr.prev_mse < prm.fit_eps) {
+        if (pr.similar >= prm.max_similar) {
+          pr.state = 4;
+          pr.converged = 1;
+          done = true;
+        }
+        is_similar = true;
+      }
+      if (!done) {
+        pr.similar = is_similar ? pr.similar + 1 : 0;
+        pr.prev_mse = mse;
+      }
+    }
+  }
+  for (int a = 0; a < 3; ++a) pr.ss[a] = pr.sd[a] = 0;
+  for (int k = 0; k < 9; ++k) pr.cov[k] = 0;
+  pr.mse_fix = 0;
+  pr.cnt = 0;
+  if (done) {
+    pr.active = 0;
+    atomicSub(n_active, 1);
+  }
+}
+
+__global__ void k_icp_finish(const PairDev* __restrict__ pairs, int n_pairs, const TreeDev* __restrict__ trees, double score_thr,
+                             loop_result* __restrict__ out) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pairs) return;
+  const PairDev& pr = pairs[p];
+  loop_result r;
+  for (int k = 0; k < 16; ++k) r.T[k] = pr.Tfinal[k];
+  r.score = pr.score_n > 0 ? ((double)pr.score_fix / kFixProd) / (double)pr.score_n : DBL_MAX;
+  r.converged = pr.converged;
+  r.valid = (pr.converged && r.score < score_thr) ? 1 : 0;
+  r.iterations = pr.iters;
+  r.state = pr.state;
+  r.n_src = (int)pr.src_n;
+  r.n_dst = (int)trees[pr.dst_job].n;
+  out[p] = r;
+}
+
+__global__ void __launch_bounds__(kBlock) k_aligned(const float4* __restrict__ src, int n, const float* __restrict__ Tfinal,
+                                                    float4* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float T[16];
+  for (int k = 0; k < 16; ++k) T[k] = Tfinal[k];
+  const float4 s = src[i];
+  float x, y, z;
+  tf_f(T, s.x, s.y, s.z, x, y, z);
+  out[i] = make_float4(x, y, z, s.w);
+}
+
+}  // namespace
+
+static uint32_t pow2_ceil(uint32_t v) {
+  uint32_t p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// builds one search tree per distinct target cloud of the batch
+static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs) {
+  const int nt = (int)tree_jobs.size();
+  cudaStream_t s = c->stream;
+  c->trees_host.assign(nt, TreeDev{});
+  std::vector<uint32_t> offs(2 * (size_t)nt + 2, 0);  // [0, nt): compact offsets, [nt, 2nt): padded offsets
+  uint32_t cmp = 0, pad = 0, node = 0;
+  for (int t = 0; t < nt; ++t) {
+    const GridDev& g = c->grids_host[tree_jobs[t]];
+    TreeDev& tr = c->trees_host[t];
+    tr.src_off = g.vox_off;
+    tr.n = g.vox_n;
+    tr.nleaf = (tr.n + kLeafPts - 1) / kLeafPts;
+    tr.nleaf_pad = std::max<uint32_t>(2u, pow2_ceil(tr.nleaf));
+    tr.pts_off = pad;
+    tr.node_off = node;
+    offs[t] = cmp;
+    offs[nt + t] = pad;
+    cmp += tr.n;
+    pad += tr.nleaf * kLeafPts;
+    node += tr.nleaf_pad;
+  }
+  int rc;
+  if ((rc = c->trees.ensure(std::max(nt, 1))) || (rc = c->blk2job.ensure(offs.size())) || (rc = c->tree_pts.ensure(std::max<uint32_t>(pad, 1))) ||
+      (rc = c->nodes.ensure(std::max<uint32_t>(node, 1))))
+    return rc;
+  if (nt == 0) return LOOP_OK;
+  LOOP_CUDA(cudaMemcpyAsync(c->trees.p, c->trees_host.data(), sizeof(TreeDev) * nt, cudaMemcpyHostToDevice, s));
+  LOOP_CUDA(cudaMemcpyAsync(c->blk2job.p, offs.data(), sizeof(uint32_t) * offs.size(), cudaMemcpyHostToDevice, s));
+  const uint32_t* cmp_off = c->blk2job.p;
+  const uint32_t* pad_off = c->blk2job.p + nt;
+  tbegin(c, LT_TREE);
+  if (cmp) {
+    if ((rc = c->keys_a.ensure(cmp)) || (rc = c->keys_b.ensure(cmp)) || (rc = c->vals_a.ensure(cmp)) || (rc = c->vals_b.ensure(cmp))) return rc;
+    int bits = 1;
+    while ((1u << bits) < (uint32_t)nt) ++bits;
+    size_t need = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, need, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)cmp, 0, 32 + bits, s);
+    need = std::max(need, sizeof(BoxAcc) * (size_t)nt);
+    if ((rc = c->cub_tmp.ensure(need))) return rc;
+    BoxAcc* acc = reinterpret_cast<BoxAcc*>(c->cub_tmp.p);
+    k_tree_box_init<<<grid_of(nt, 128), 128, 0, s>>>(acc, nt);
+    k_tree_box<<<grid_of(cmp, kBlock), kBlock, 0, s>>>(c->trees.p, cmp_off, nt, cmp, c->vox.p, acc);
+    k_tree_keys<<<grid_of(cmp, kBlock), kBlock, 0, s>>>(c->trees.p, cmp_off, nt, cmp, c->vox.p, acc, c->keys_a.p, c->vals_a.p);
+    size_t bytes = c->cub_tmp.cap;
+    LOOP_CUDA(cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, bytes, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)cmp, 0, 32 + bits, s));
+    c->launches += 4;
+  }
+  if (pad) {
+    k_tree_gather<<<grid_of(pad, kBlock), kBlock, 0, s>>>(c->trees.p, nt, cmp_off, pad_off, pad, c->vals_b.p, c->vox.p, c->tree_pts.p);
+    c->launches += 1;
+  }
+  k_tree_nodes<<<nt, 1024, 0, s>>>(c->trees.p, c->tree_pts.p, c->nodes.p);
+  c->launches += 1;
+  tend(c);
+  LOOP_CUDA(cudaGetLastError());
+  // offs / trees_host feed async copies: keep them alive until the copies are done
+  LOOP_CUDA(cudaStreamSynchronize(s));
+  return LOOP_OK;
+}
+
+int run_icp(loop_ctx* c, const std::vector<PairHost>& ph, double score_thr, loop_result* out) {
+  const int np = (int)ph.size();
+  c->n_pairs = np;
+  c->st_iters = c->st_src = c->st_queries = 0;
+  if (np == 0) return LOOP_OK;
+  cudaStream_t s = c->stream;
+  // distinct target clouds -> trees
+  std::vector<int> tree_of_job(c->n_jobs, -1), tree_jobs;
+  for (const PairHost& p : ph)
+    if (tree_of_job[p.dst_job] < 0) {
+      tree_of_job[p.dst_job] = (int)tree_jobs.size();
+      tree_jobs.push_back(p.dst_job);
+    }
+  int rc = build_trees(c, tree_jobs);
+  if (rc) return rc;
+
+  c->pairs_host.assign(np, PairDev{});
+  std::vector<uint32_t> b2p;
+  uint64_t cur_total = 0;
+  for (int p = 0; p < np; ++p) {
+    PairDev& pr = c->pairs_host[p];
+    const GridDev& g = c->grids_host[ph[p].src_job];
+    pr.src_off = g.vox_off;
+    pr.src_n = g.vox_n;
+    pr.dst_job = (uint32_t)tree_of_job[ph[p].dst_job];
+    pr.cur_off = (uint32_t)cur_total;
+    for (int k = 0; k < 16; ++k) pr.Tr[k] = pr.Tfinal[k] = (k % 5 == 0) ? 1.f : 0.f;
+    pr.prev_mse = DBL_MAX;
+    pr.active = 1;
+    for (uint32_t b = 0; b < pr.src_n; b += kBlock) {
+      b2p.push_back((uint32_t)p);
+      b2p.push_back(b);
+    }
+    cur_total += pr.src_n;
+  }
+  if (cur_total >= 0xFFFFFFFFull) {
+    lio::set_error("batch chunk holds %llu source points (limit 2^32-1)", (unsigned long long)cur_total);
+    return LOOP_E_CAPACITY;
+  }
+  const int n_blocks = (int)(b2p.size() / 2);
+  if ((rc = c->pairs.ensure(np)) || (rc = c->blk2pair.ensure(std::max<size_t>(b2p.size(), 2))) || (rc = c->cur.ensure(std::max<uint64_t>(cur_total, 1))) ||
+      (rc = c->match.ensure(std::max<uint64_t>(cur_total, 1))) || (rc = c->md2.ensure(std::max<uint64_t>(cur_total, 1))))
+    return rc;
+  LOOP_CUDA(cudaMemcpyAsync(c->pairs.p, c->pairs_host.data(), sizeof(PairDev) * np, cudaMemcpyHostToDevice, s));
+  if (n_blocks) LOOP_CUDA(cudaMemcpyAsync(c->blk2pair.p, b2p.data(), sizeof(uint32_t) * b2p.size(), cudaMemcpyHostToDevice, s));
+  *c->active_host = np;
+  LOOP_CUDA(cudaMemcpyAsync(c->active_dev, c->active_host, sizeof(int), cudaMemcpyHostToDevice, s));
+  LOOP_CUDA(cudaStreamSynchronize(s));  // b2p / pairs_host are host temporaries
+
+  const IcpParams& prm = c->prm;
+  for (int it = 0; it < prm.max_iter; ++it) {
+    if (n_blocks) {
+      tbegin(c, LT_NN);
+      k_icp_nn<0><<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->md2.p, c->trees.p, c->nodes.p,
+                                             c->tree_pts.p, prm.max_d2);
+      tend(c);
+      tbegin(c, LT_COV);
+      k_icp_cov<<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->trees.p, prm.min_corr);
+      tend(c);
+      c->launches += 2;
+    }
+    tbegin(c, LT_SOLVE);
+    k_icp_solve<<<grid_of(np, 64), 64, 0, s>>>(c->pairs.p, np, prm, c->active_dev);
+    tend(c);
+    c->launches += 1;
+    if ((it & 3) == 3 || it == prm.max_iter - 1) {
+      LOOP_CUDA(cudaMemcpyAsync(c->active_host, c->active_dev, sizeof(int), cudaMemcpyDeviceToHost, s));
+      LOOP_CUDA(cudaStreamSynchronize(s));
+      if (*c->active_host <= 0) break;
+    }
+  }
+  if (n_blocks) {
+    tbegin(c, LT_SCORE);
+    k_icp_nn<1><<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->md2.p, c->trees.p, c->nodes.p,
+                                           c->tree_pts.p, prm.max_d2);
+    tend(c);
+    c->launches += 1;
+  }
+  // results: staged in the (now free) md2 head? no - md2 is part of the debug getters; use a dedicated small buffer in keys_a
+  if ((rc = c->keys_a.ensure((sizeof(loop_result) * (size_t)np + 7) / 8))) return rc;
+  loop_result* res_dev = reinterpret_cast<loop_result*>(c->keys_a.p);
+  k_icp_finish<<<grid_of(np, 64), 64, 0, s>>>(c->pairs.p, np, c->trees.p, score_thr, res_dev);
+  c->launches += 1;
+  LOOP_CUDA(cudaGetLastError());
+  LOOP_CUDA(cudaMemcpyAsync(out, res_dev, sizeof(loop_result) * (size_t)np, cudaMemcpyDeviceToHost, s));
+  LOOP_CUDA(cudaMemcpyAsync(c->pairs_host.data(), c->pairs.p, sizeof(PairDev) * np, cudaMemcpyDeviceToHost, s));
+  LOOP_CUDA(cudaStreamSynchronize(s));
+  for (int p = 0; p < np; ++p) {
+    c->st_iters += out[p].iterations;
+    c->st_src += out[p].n_src;
+    c->st_queries += (int64_t)out[p].n_src * (out[p].iterations + (out[p].state == 5 ? 1 : 0) + 1);
+  }
+  return LOOP_OK;
+}
+
+int fetch_aligned(loop_ctx* c, int pair, float* out, int cap, int* n_out) {
+  const PairDev& pr = c->pairs_host[pair];
+  if (n_out) *n_out = (int)pr.src_n;
+  const int n = std::min<int>(cap, (int)pr.src_n);
+  if (n <= 0 || !out) return LOOP_OK;
+  int rc;
+  if ((rc = c->raw.ensure(pr.src_n))) return rc;
+  k_aligned<<<grid_of(pr.src_n, kBlock), kBlock, 0, c->stream>>>(c->vox.p + pr.src_off, (int)pr.src_n, c->pairs.p[pair].Tfinal, c->raw.p);
+  c->launches += 1;
+  LOOP_CUDA(cudaGetLastError());
+  LOOP_CUDA(cudaMemcpyAsync(out, c->raw.p, sizeof(float4) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  LOOP_CUDA(cudaStreamSynchronize(c->stream));
+  return LOOP_OK;
+}
+
+int fetch_corr(loop_ctx* c, int pair, int* out) {
+  const PairDev& pr = c->pairs_host[pair];
+  if (!pr.src_n) return LOOP_OK;
+  LOOP_CUDA(cudaMemcpyAsync(out, c->match.p + pr.cur_off, sizeof(int) * (size_t)pr.src_n, cudaMemcpyDeviceToHost, c->stream));
+  LOOP_CUDA(cudaStreamSynchronize(c->stream));
+  return LOOP_OK;
+}
+
+}  // namespace loopb

@@ -16,30 +16,11 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include "loop_ctx.h"
+#include "loop_device.cuh"
 
 namespace loopb {
 
 namespace {
-
-__device__ __forceinline__ uint32_t f2ord(float f) {
-  const uint32_t b = __float_as_uint(f);
-  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
-__host__ __device__ __forceinline__ float ord2f(uint32_t u) {
-  const uint32_t b = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u;
-#ifdef __CUDA_ARCH__
-  return __uint_as_float(b);
-#else
-  float f;
-  memcpy(&f, &b, 4);
-  return f;
-#endif
-}
-
-// per-job reduction cells: 6 ordered-uint box bounds + finite count
-struct BoxAcc {
-  uint32_t lo[3], hi[3], n_finite, pad;
-};
 
 __global__ void k_box_init(BoxAcc* acc, int n_jobs) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;

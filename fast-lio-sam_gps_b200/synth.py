@@ -232,3 +232,44 @@ def street_poses(n, scene, z=1.8, seed=SEED + 4, step=0.5, pitch=20.0):
         R = rot_from_rpy(rng.uniform(-0.02, 0.02), rng.uniform(-0.02, 0.02), rng.uniform(-0.1, 0.1) + 0.01 * i)
         out.append((R, np.array([x, y, z])))
     return out
+
+
+def pose44(R, t):
+    T = np.eye(4)
+    T[:3, :3] = R
+    T[:3, 3] = t
+    return T
+
+
+def make_keyframes(scene, n_pass=40, step=1.0, kind="vlp16", n_az=None, max_range=60.0, seed=SEED + 200, drift_t=(0.6, -0.5, 0.1),
+                   drift_rpy_deg=(0.5, -0.4, 2.0), walk=0.01, lateral=0.4, z=1.8, start_x=None):
+    """Keyframes of an out-and-back drive along the free x-axis street: pass 1 (indices 0..n_pass-1) outward, pass 2
+    (n_pass..2*n_pass-1) back over the same ground, so every pass-2 keyframe has loop candidates in pass 1.
+
+    Returns (clouds, poses_est, poses_true, stamps): clouds[i] is an (n, 4) float32 xyzi cloud in the LiDAR frame
+    (PosePcd::pcd_, pose_pcd.hpp:39); poses_est are the pose_corrected_eig_ the loop closer sees: exact on pass 1, true pose
+    composed with a slowly wandering drift (about drift_t metres / drift_rpy_deg degrees) on pass 2; stamps 1 s apart."""
+    rng = np.random.default_rng(seed)
+    x0 = -0.3 * scene["half_extent"] if start_x is None else start_x
+    clouds, est, true, stamps = [], [], [], []
+    D = pose44(rot_from_rpy(*np.deg2rad(drift_rpy_deg)), np.asarray(drift_t, float))
+    for i in range(2 * n_pass):
+        back = i >= n_pass
+        k = (2 * n_pass - 1 - i) if back else i
+        x = x0 + step * k
+        y = (lateral if back else 0.0) + 0.05 * np.sin(0.3 * k)
+        yaw = (np.pi if back else 0.0) + 0.02 * np.sin(0.2 * k)
+        R = rot_from_rpy(0.005 * np.sin(0.5 * k), 0.005 * np.cos(0.4 * k), yaw)
+        t = np.array([x, y, z])
+        pts = make_scan(scene, R, t, kind=kind, n_az=n_az, seed=seed + 1 + i, max_range=max_range)
+        inten = rng.uniform(0, 255, (len(pts), 1)).astype(np.float32)
+        clouds.append(np.ascontiguousarray(np.concatenate([pts, inten], 1)))
+        T = pose44(R, t)
+        true.append(T)
+        if back:
+            D = D @ pose44(so3_exp(rng.normal(0, walk * 0.2, 3)), rng.normal(0, walk, 3))
+            est.append(D @ T)
+        else:
+            est.append(T.copy())
+        stamps.append(float(i))
+    return clouds, est, true, stamps
