@@ -196,6 +196,15 @@ def test_map_delete_boxes_parity(pkg, orc):
     g.close()
 
 
+def _predict(state, dR, dt):
+    """state (+) body-frame motion (dR, dt): pos += rot*dt, rot = rot*dR  (state layout of include/lio_b200.h)."""
+    s = state.copy()
+    Rw = s[3:12].reshape(3, 3)
+    s[0:3] = s[0:3] + Rw @ dt
+    s[3:12] = (Rw @ dR).reshape(9)
+    return s
+
+
 def test_sequence_with_map_growth_ate(pkg, orc, synth):
     """Config-1/3 shaped slice: scans along a street, IEKF update + map_incremental every scan, local-map cube moving.
     Two GPU contexts against one oracle:
@@ -217,10 +226,17 @@ def test_sequence_with_map_growth_ate(pkg, orc, synth):
     fP = oP = synth.default_cov()
     Q = np.eye(23) * 1e-3
     traj_f, traj_o = [], []
+    pred_rng = np.random.default_rng(77)
     for i, (R, t) in enumerate(poses[1:], 1):
         kind = "avia" if i % 2 else "vlp16"
         scan = synth.make_scan(scene, R, t, kind=kind, seed=100 + i, phase=0.37 * i)
-        fP, oP = fP + Q, oP + Q  # constant-position prediction: start from the previous estimate, inflate P
+        # IMU-like prediction (forward propagation is outside the hot path): compose the previous
+        # estimate with the true relative motion plus a 2 cm / 0.2 deg error, inflate P
+        Rp, tp = poses[i - 1]
+        dR = Rp.T @ R @ synth.so3_exp(pred_rng.normal(0, 0.0035, 3))
+        dt = Rp.T @ (t - tp) + pred_rng.normal(0, 0.02, 3)
+        fs, os_ = _predict(fs, dR, dt), _predict(os_, dR, dt)
+        fP, oP = fP + Q, oP + Q
         ob = o.fov_segment(os_[:3])
         assert np.array_equal(g.fov_segment(os_[:3]), ob)
         f.fov_segment(fs[:3])
@@ -244,7 +260,7 @@ def test_sequence_with_map_growth_ate(pkg, orc, synth):
     ate = np.sqrt(np.mean(np.sum((np.array(traj_f) - np.array(traj_o)) ** 2, 1)))
     assert ate < 1e-3
     truth = np.array([t for _, t in poses[1:]])
-    assert np.sqrt(np.mean(np.sum((np.array(traj_f) - truth) ** 2, 1))) < 0.05
+    assert np.sqrt(np.mean(np.sum((np.array(traj_f) - truth) ** 2, 1))) < 0.08  # tracks ground truth too
     g.close()
     f.close()
 
