@@ -45,6 +45,10 @@ def parse():
     ap.add_argument("--n-scan", type=int, default=N_SCAN)
     ap.add_argument("--n-map", type=int, default=N_MAP)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pairs", type=int, default=256, help="loop workload: candidate pairs in the batch")
+    ap.add_argument("--submap-range", type=int, default=12, help="loop workload: R (2R+1 keyframes per side)")
+    ap.add_argument("--n-pass", type=int, default=100, help="loop workload: keyframes per pass of the out-and-back drive")
+    ap.add_argument("--no-loop", action="store_true", help="iekf workload: skip the loop_icp section of the JSON line")
     return ap.parse_args()
 
 
@@ -262,6 +266,13 @@ def run_ours(args, synth):
     value = total_scans / (dev_ms * 1e-3)
     e2e = total_scans / (e2e_ms * 1e-3)
 
+    loop_out = None
+    if not args.no_loop:  # configs[3] in the same run: pairs sharded over the ranks, host gather only
+        loop_mod = importlib.import_module("fast-lio-sam_gps_b200.loop")
+        loop_bench = importlib.import_module("fast-lio-sam_gps_b200.loop_bench")
+        loop_out = loop_bench.loop_section(synth, loop_mod, rank, local_rank, world, args.pairs, 2, 1, submap_range=args.submap_range,
+                                           n_pass=args.n_pass, cpu_pairs=0 if (args.no_cpu_baseline or world > 1) else 16, stream=stream)
+
     if rank == 0:
         peaks = {}
         try:
@@ -296,6 +307,8 @@ def run_ours(args, synth):
             line["cpu_baseline"] = {"value": r["scans_per_s"], "unit": "scans/s", "cores": r["cores"], "kind": "port",
                                     "sample": f"{max(2, min(6, args.steps))} full scans of the same workload (oracle port, OpenMP, all host cores)",
                                     "ms_per_step": r["ms_per_step"]}
+        if loop_out is not None:
+            line["loop_icp"] = loop_out
         print(json.dumps(line))
     g.close()
     if world > 1:

@@ -1,0 +1,213 @@
+"""Loop-closure ICP workload of BASELINE.json configs[3]: a batch of candidate pairs, each side a voxelised submap of
+2R+1 keyframes (R = 12 -> 25 keyframes, the BASELINE shape; R = 5 is the reference's own default, fast_lio_sam.cpp:69),
+ICP constants of loop_closure.cpp:7-11, max correspondence distance 52.5 m (fast_lio_sam.cpp:73), leaf 0.3 m
+(config.yaml:15).  Pairs are independent (loop_closure.cpp:101-126) -> sharded contiguously over ranks, host gather only."""
+import ctypes as C
+import json
+import os
+import time
+
+import numpy as np
+
+
+def shard_pairs(n_pairs, rank, world):
+    """Contiguous slice [lo, hi) of the pair list owned by `rank` (sizes differ by at most one)."""
+    base, rem = divmod(n_pairs, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def make_loop_workload(synth, n_pairs=256, n_pass=100, n_az=1800, submap_range=12, seed=None):
+    """Out-and-back drive; pair = (pass-2 keyframe, its pass-1 counterpart shifted by -1/0/+1).  The drift of pass 2 is
+    ~1 m / 3 deg."""
+    seed = synth.SEED + 200 if seed is None else seed
+    half = max(80.0, 0.9 * n_pass)
+    scene = synth.make_scene(half_extent=half)
+    clouds, est, true, stamps = synth.make_keyframes(scene, n_pass=n_pass, step=1.0, n_az=n_az, max_range=60.0, seed=seed,
+                                                     drift_t=(0.6, -0.5, 0.1), drift_rpy_deg=(0.5, -0.4, 2.0), start_x=-0.5 * n_pass)
+    K = 2 * n_pass
+    pairs = []
+    lo, hi = n_pass + submap_range, K - 2 - submap_range  # keep both submaps full (the newest keyframe is excluded: size-2)
+    for off in (0, -1, 1, -2, 2):
+        for s in range(hi, lo - 1, -1):
+            d = (K - 1 - s) + off
+            if submap_range <= d < n_pass - submap_range and len(pairs) < n_pairs:
+                pairs.append((s, d))
+    if len(pairs) < n_pairs:
+        raise ValueError(f"only {len(pairs)} distinct pairs available for n_pass={n_pass}, R={submap_range}")
+    return dict(clouds=clouds, est=est, true=true, stamps=stamps, pairs=pairs[:n_pairs], range=submap_range)
+
+
+def cpu_loop(orc, w, pairs, leaf, score_thr, max_corr, threads):
+    """Oracle (restatement of setSrcAndDstCloud + VoxelGrid + pcl::IterativeClosestPoint), pair-parallel over `threads`."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    o = orc.OracleLoop(max_corr_dist=max_corr, nthreads=1)
+    for c, e, s in zip(w["clouds"], w["est"], w["stamps"]):
+        o.add_keyframe(c, e, s)
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=threads) as ex:  # ctypes releases the GIL inside the C call
+        res = list(ex.map(lambda p: o.verify(p[0], p[1], w["range"], leaf, score_thr), pairs))
+    dt = time.perf_counter() - t0
+    o.close()
+    return res, dt
+
+
+LEAF, SCORE_THR, RADIUS = 0.3, 1.5, 35.0  # config.yaml:15,12,8 (effective values)
+ICP_ALGO_BYTES = 32  # per source point per correspondence pass: 16 B source + 16 B matched target
+
+
+def gpu_loop(loop_mod, w, pairs, device=0, steps=3, warmup=1, stream=None):
+    """loop_verify_batch on this rank's slice.  Returns (results of the last step, mean ms/step from CUDA events on the
+    context's stream, per-kernel-family times, stats, launches per step).  The keyframe store is resident (uploaded once,
+    like keyframes_ in the reference); the timed region is the whole C-ABI call: submap build + VoxelGrid + ICP + D2H."""
+    import torch
+
+    g = loop_mod.LoopClosure(num_submap_keyframes=w["range"], voxel_res=LEAF, loop_detection_radius=RADIUS, icp_score_threshold=SCORE_THR,
+                             device=device, stream=stream.cuda_stream if stream is not None else None)
+    for c, e, s in zip(w["clouds"], w["est"], w["stamps"]):
+        g.add_keyframe(c, e, s)
+    n = len(pairs)
+    arr = (loop_mod.LoopPair * max(n, 1))()
+    for i, (a, b) in enumerate(pairs):
+        arr[i].src_idx, arr[i].dst_idx = int(a), int(b)
+    res = (loop_mod.LoopResult * max(n, 1))()
+    st = stream if stream is not None else torch.cuda.current_stream()
+    for _ in range(warmup):
+        g.verify_batch_raw(arr, n, res)
+    l0 = g.launch_count()
+    evs = []
+    for _ in range(steps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(st)
+        g.verify_batch_raw(arr, n, res)
+        b.record(st)
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in evs) / max(steps, 1)
+    launches = (g.launch_count() - l0) / max(steps, 1)
+    g.timing(True)  # one extra, untimed-by-the-bench pass with per-kernel CUDA events (they serialise the launches)
+    g.timing_reset()
+    g.verify_batch_raw(arr, n, res)
+    kt = {k: g.timing_get(k) for k in ("submap", "voxel", "tree", "nn", "cov", "solve", "score")}
+    stats = g.batch_stats()
+    out = [loop_mod._result(res[i]) for i in range(n)]
+    g.timing(False)
+    g.close()
+    return out, ms, kt, stats, launches
+
+
+def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmup, submap_range=12, n_pass=100, n_az=1800,
+                 cpu_pairs=0, stream=None):
+    """Runs config 4 on `world` ranks (pairs sharded, no data-path collective) and returns the dict rank 0 reports."""
+    import torch
+    import torch.distributed as dist
+
+    w = make_loop_workload(synth, n_pairs=n_pairs, n_pass=n_pass, n_az=n_az, submap_range=submap_range)
+    lo, hi = shard_pairs(n_pairs, rank, world)
+    mine = w["pairs"][lo:hi]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    res, ms, kt, stats, launches = gpu_loop(loop_mod, w, mine, device=local_rank, steps=steps, warmup=warmup, stream=stream)
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    gathered = [res]
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)  # device-timed, max over ranks
+        gathered = [None] * world
+        dist.all_gather_object(gathered, [(r["valid"], r["converged"], r["iterations"], float(r["score"])) for r in res])  # host gather
+    ms_max = float(t.item())
+    if rank != 0:
+        return None
+    flat = [x for part in gathered for x in part]
+    nn_ms, nn_n = kt["nn"]
+    sc_ms, sc_n = kt["score"]
+    q = stats["nn_queries"]
+    peak = _peak()
+    achieved = ICP_ALGO_BYTES * q / ((nn_ms + sc_ms) * 1e-3) / 1e9 if nn_ms + sc_ms > 0 else 0.0
+    out = {
+        "metric": "loop-ICP pairs/s", "value": n_pairs / (ms_max * 1e-3), "unit": "pairs/s", "n_gpus": world, "ms_per_batch": ms_max,
+        "pairs": n_pairs, "pairs_rank0": hi - lo, "scaling": "strong", "submap_keyframes_per_side": 2 * submap_range + 1,
+        "points_per_keyframe": int(np.mean([len(c) for c in w["clouds"]])), "voxel_res": LEAF, "max_corr_dist": RADIUS * 1.5,
+        "results_gathered": len(flat),
+        "rank0": {"valid": int(sum(bool(r["valid"]) for r in res)), "converged": int(sum(bool(r["converged"]) for r in res)),
+                  "mean_iterations": stats["iterations"] / max(len(res), 1), "mean_src_points": stats["src_points"] / max(len(res), 1),
+                  "gpu_launches_per_batch": launches,
+                  "kernel_ms": {k: {"total_ms": v[0], "launches": v[1]} for k, v in kt.items()}},
+        "roofline": {"bound": "hbm", "kernel": "k_icp_nn (transform + exact 1-NN, all pairs per launch)", "achieved": achieved,
+                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "algorithmic_bytes": ICP_ALGO_BYTES * q, "kernel_ms_total": nn_ms + sc_ms, "launches_timed": nn_n + sc_n},
+    }
+    if cpu_pairs > 0:
+        from oracle import orc
+
+        orc.build()
+        cores = orc.max_threads()
+        sample = w["pairs"][:cpu_pairs]
+        cres, dt = cpu_loop(orc, w, sample, LEAF, SCORE_THR, RADIUS * 1.5, cores)
+        same = all(np.array_equal(a["T"], b["T"]) and a["score"] == b["score"] and a["iterations"] == b["iterations"]
+                   for a, b in zip(cres, res[: len(sample)]))
+        out["cpu_baseline"] = {"value": len(sample) / dt, "unit": "pairs/s", "cores": min(cores, len(sample)), "kind": "port",
+                               "sample": f"first {len(sample)} pairs of the batch, one oracle ICP per thread (PCL's ICP is "
+                                         f"single-threaded per pair as called at loop_closure.cpp:79-81)",
+                               "bit_identical_to_gpu": bool(same)}
+    return out
+
+
+def _peak():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    try:
+        return float(json.load(open(os.path.join(root, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6650.0
+
+
+def main(args):
+    """`bench.py --workload loop [--impl reference]`: config 4 as a standalone run (one JSON line from rank 0)."""
+    import importlib
+
+    synth = importlib.import_module("fast-lio-sam_gps_b200.synth")
+    rank, local_rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    n_pairs, R = args.pairs, args.submap_range
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        from oracle import orc
+
+        orc.build()
+        w = make_loop_workload(synth, n_pairs=n_pairs, n_pass=args.n_pass, submap_range=R)
+        cores = orc.max_threads()
+        sample = w["pairs"][: max(cores, min(n_pairs, 2 * cores))]
+        _, dt = cpu_loop(orc, w, sample, LEAF, SCORE_THR, RADIUS * 1.5, cores)
+        v = len(sample) / dt
+        print(json.dumps({"impl": "reference", "metric": "loop-ICP pairs/s", "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
+                          "steps": 1, "warmup": 0, "ms_per_step": 1e3 * dt, "higher_is_better": True, "scaling": "strong",
+                          "vs_baseline": None, "dtype": "f32 points, f64 poses/score", "data": "synthetic",
+                          "config": {"workload": "configs[3]: batched loop-closure ICP verification", "pairs": n_pairs,
+                                     "submap_keyframes_per_side": 2 * R + 1},
+                          "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
+                                           "sample": f"{len(sample)} pairs, one oracle ICP per thread"},
+                          "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+        return
+    import torch
+    import torch.distributed as dist
+
+    loop_mod = importlib.import_module("fast-lio-sam_gps_b200.loop")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    stream = torch.cuda.Stream()
+    out = loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, args.steps, max(1, args.warmup), submap_range=R,
+                       n_pass=args.n_pass, cpu_pairs=0 if (args.no_cpu_baseline or world > 1) else 16, stream=stream)
+    if rank == 0:
+        out.update({"steps": args.steps, "warmup": max(1, args.warmup), "ms_per_step": out["ms_per_batch"], "higher_is_better": True,
+                    "vs_baseline": None, "dtype": "f32 points, f64 poses/score, exact fixed-point reductions", "data": "synthetic",
+                    "config": {"workload": "configs[3]: batched loop-closure ICP verification (keyframe store resident, whole "
+                                           "loop_verify_batch C-ABI call timed incl. result D2H)", "pairs": n_pairs,
+                               "submap_keyframes_per_side": 2 * R + 1, "parallelism": f"pairs sharded over {world} GPU(s), host gather"},
+                    "gpu_launches": int(out["rank0"]["gpu_launches_per_batch"] * args.steps)})
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
