@@ -269,7 +269,7 @@ def run_ours(args, synth):
     loop_out = None
     if not args.no_loop:  # configs[3] in the same run: pairs sharded over the ranks, host gather only
         loop_mod = importlib.import_module("fast-lio-sam_gps_b200.loop")
-        loop_bench = importlib.import_module("fast-lio-sam_gps_b200.loop_bench")
+        loop_bench = importlib.import_module("bench_loop")
         loop_out = loop_bench.loop_section(synth, loop_mod, rank, local_rank, world, args.pairs, 2, 1, submap_range=args.submap_range,
                                            n_pass=args.n_pass, cpu_pairs=0 if (args.no_cpu_baseline or world > 1) else 16, stream=stream)
 
@@ -319,7 +319,7 @@ def main():
     args = parse()
     synth = importlib.import_module("fast-lio-sam_gps_b200.synth")
     if args.workload == "loop":
-        loop_bench = importlib.import_module("fast-lio-sam_gps_b200.loop_bench")
+        loop_bench = importlib.import_module("bench_loop")
         return loop_bench.main(args)
     if args.impl == "reference":
         return run_reference(args, synth)

@@ -11,10 +11,9 @@ import numpy as np
 
 
 def shard_pairs(n_pairs, rank, world):
-    """Contiguous slice [lo, hi) of the pair list owned by `rank` (sizes differ by at most one)."""
-    base, rem = divmod(n_pairs, world)
-    lo = rank * base + min(rank, rem)
-    return lo, lo + base + (1 if rank < rem else 0)
+    import importlib
+
+    return importlib.import_module("fast-lio-sam_gps_b200.loop").shard_pairs(n_pairs, rank, world)
 
 
 def make_loop_workload(synth, n_pairs=256, n_pass=100, n_az=1800, submap_range=12, seed=None):
@@ -155,7 +154,7 @@ def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmu
 
 
 def _peak():
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    root = os.path.dirname(os.path.abspath(__file__))
     try:
         return float(json.load(open(os.path.join(root, "MEASURED_PEAKS.json")))["hbm_gbs"])
     except Exception:

@@ -93,6 +93,7 @@ LIO_SYMBOLS = {
     "lio_timing_enable": (C.c_int, [C.c_void_p, C.c_int]),
     "lio_timing_get": (C.c_int, [C.c_void_p, C.c_char_p, _f64p, _i32p]),
     "lio_timing_reset": (C.c_int, [C.c_void_p]),
+    "lio_knn_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "lio_launch_count": (C.c_int64, [C.c_void_p]),
 }
 
@@ -288,6 +289,11 @@ class LioContext:
         ms, n = C.c_double(0), C.c_int(0)
         self._check(self.lib.lio_timing_get(self.h, name.encode(), C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def knn_fallback_queries(self):
+        v = C.c_uint64(0)
+        self._check(self.lib.lio_knn_stats(self.h, C.byref(v)))
+        return int(v.value)
 
     def launch_count(self):
         return int(self.lib.lio_launch_count(self.h))

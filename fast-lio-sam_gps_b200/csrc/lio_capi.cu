@@ -320,6 +320,7 @@ int lio_scan_upload(lio_ctx* c, const float* body_xyz, int n) {
   }
   c->scan_n = n;
   c->nn_valid = false;
+  c->order_valid = false;
   if (n == 0) return LIO_OK;
   return upload_xyz(c, body_xyz, n, c->body);
 }
@@ -333,6 +334,7 @@ int lio_scan_set_device(lio_ctx* c, const void* body_xyzw_dev, int n) {
   }
   c->scan_n = n;
   c->nn_valid = false;
+  c->order_valid = false;
   if (n == 0) return LIO_OK;
   LIO_CUDA(cudaMemcpyAsync(c->body, body_xyzw_dev, sizeof(float4) * (size_t)n, cudaMemcpyDeviceToDevice, c->stream));
   return LIO_OK;
@@ -574,6 +576,16 @@ int lio_timing_reset(lio_ctx* c) {
     c->t_sum[i] = 0;
     c->t_n[i] = 0;
   }
+  return LIO_OK;
+}
+
+int lio_knn_stats(lio_ctx* c, uint64_t* fallback_queries) {
+  int rc = check_ctx(c);
+  if (rc) return rc;
+  uint32_t v[4] = {0, 0, 0, 0};
+  LIO_CUDA(cudaMemcpyAsync(v, c->tile_stats, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+  LIO_CUDA(cudaStreamSynchronize(c->stream));
+  if (fallback_queries) *fallback_queries = v[0];
   return LIO_OK;
 }
 

@@ -74,6 +74,16 @@ struct lio_ctx {
   uint32_t* blk_cnt = nullptr;  // per-block counts for the ordered compaction (2 x blocks)
   float4* list_add = nullptr;
   float4* list_nodown = nullptr;
+  // tile kNN: Morton order of the scan (lio_knn_tile.cuh)
+  uint32_t* tile_keys[2] = {nullptr, nullptr};
+  uint32_t* tile_vals[2] = {nullptr, nullptr};
+  void* tile_tmp = nullptr;
+  size_t tile_tmp_bytes = 0;
+  uint32_t tile_cap = 0;
+  bool order_valid = false;      // tile_vals[1] holds the order of the current scan
+  uint32_t* tile_stats = nullptr;  // [0] queries that went to the per-query fallback (debug/bench counter)
+  int tile_flip = 0;             // which counter pair the next search uses
+  int knn_mode = 1;              // 1 tile (default), 0 per-query groups (LIO_KNN_MODE=group)
   double* state_dev = nullptr;  // 36 doubles
   double* partials = nullptr;   // reduction partials
   int partial_blocks = 0;
@@ -118,6 +128,7 @@ int scan_knn(lio_ctx* c, const double* state_host);
 int scan_plane_reduce(lio_ctx* c, const double* state_host, bool want_rows);
 int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inited);
 int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float4* out_nn, float* out_d2, int* out_cnt);
+int tile_ensure(lio_ctx* c, uint32_t n);
 
 // timing helpers (lio_capi.cu)
 void timer_begin(lio_ctx* c, int id);

@@ -110,6 +110,48 @@ __device__ __forceinline__ void merge_top(const Group<G>& g, TopList& L, unsigne
   }
 }
 
+// Scans the chains of up to 32 hit cells: bit b of `hits` = the cell probed by lane (b % G) in slot (b / G) of raw[].
+// Bucket loads are issued four at a time before any is consumed, so a query waits for ~hits/4 memory round trips
+// instead of one per cell.  G == 8 only (one bucket per load instruction).
+template <int G, int NR>
+__device__ __forceinline__ void scan_hits(const MapView& m, const Group<G>& g, unsigned hits, const uint4 (&raw)[NR], float qx, float qy,
+                                          float qz, uint32_t max_bits, TopList& L) {
+  static_assert(G == 8 && NR <= 4, "scan_hits: one bucket per 8-lane load");
+  while (hits) {
+    uint32_t hd[4], ov[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      hd[u] = ov[u] = kNone;
+      if (hits) {
+        const int b = __ffs(hits) - 1;
+        hits &= hits - 1;
+        const int r = b / G, src = b % G;
+        uint32_t z = raw[0].z, w = raw[0].w;
+#pragma unroll
+        for (int t = 1; t < NR; ++t) {
+          z = (r == t) ? raw[t].z : z;
+          w = (r == t) ? raw[t].w : w;
+        }
+        hd[u] = g.shfl(z, src);
+        ov[u] = g.shfl(w, src);
+      }
+    }
+    float4 p[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (hd[u] != kNone) p[u] = __ldg(m.slots + hd[u] * kSlots + g.gl);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (hd[u] != kNone) {
+        const uint32_t id = __float_as_uint(p[u].w);
+        const float d2 = sqdist3(qx, qy, qz, p[u].x, p[u].y, p[u].z);
+        if (id != kEmptyId && d2 <= __uint_as_float(max_bits))
+          L.insert(((unsigned long long)__float_as_uint(d2) << 32) | id, hd[u] * kSlots + g.gl);
+        if (ov[u] != kNone) scan_chain<G>(m, g, ov[u], __ldg(m.next + ov[u]), qx, qy, qz, max_bits, L);  // overflow buckets: rare
+      }
+  }
+}
+
 template <int G>
 __device__ void knn_search(const MapView& m, const Group<G>& g, float qx, float qy, float qz, float max_d2,
                            unsigned long long& okey, uint32_t& oref, int& cnt) {
@@ -133,6 +175,7 @@ __device__ void knn_search(const MapView& m, const Group<G>& g, float qx, float 
     if (idx < 27) raw[r] = __ldg(reinterpret_cast<const uint4*>(m.table + slot[r]));
     else raw[r] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, kNone, kNone);
   }
+  unsigned all_hits = 0;
 #pragma unroll
   for (int r = 0; r < NR; ++r) {
     unsigned long long ek = ((unsigned long long)raw[r].y << 32) | raw[r].x;
@@ -143,6 +186,10 @@ __device__ void knn_search(const MapView& m, const Group<G>& g, float qx, float 
     }
     const bool hit = (ek == keys[r]) && (g.gl + r * G < 27);
     unsigned hits = g.ballot(hit);
+    if (G == 8) {
+      all_hits |= hits << (r * G);
+      continue;
+    }
     while (hits) {
       // hand one chain to each sub-group of 8 lanes
       uint32_t head = kNone, ovf = kNone;
@@ -161,6 +208,7 @@ __device__ void knn_search(const MapView& m, const Group<G>& g, float qx, float 
       scan_chain<G>(m, g, head, ovf, qx, qy, qz, max_bits, L);
     }
   }
+  if constexpr (G == 8) scan_hits<G, NR>(m, g, all_hits, raw, qx, qy, qz, max_bits, L);
   merge_top<G>(g, L, okey, oref, cnt);
 
   // ---- rings 2.. : only while the answer could still change ------------------------------------------
@@ -178,6 +226,39 @@ __device__ void knn_search(const MapView& m, const Group<G>& g, float qx, float 
     L.clear();
     if (g.gl < cnt) L.insert(okey, oref);
     const int side = 2 * ring + 1, total = side * side * side;
+    if constexpr (G == 8) {
+      // four probe rounds (32 cells) in flight per step
+      for (int idx0 = 0; idx0 < total; idx0 += 4 * G) {
+        unsigned long long key4[4];
+        uint32_t slot4[4];
+        uint4 raw4[4];
+        bool want4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int idx = idx0 + u * G + g.gl;
+          const int dz = idx / (side * side) - ring, dy = (idx / side) % side - ring, dx = idx % side - ring;
+          bool want = idx < total && max(max(abs(dx), abs(dy)), abs(dz)) == ring;
+          if (want) want = cell_box_d2(qx, qy, qz, cx + dx, cy + dy, cz + dz, h) * 0.9999f <= tau;
+          want4[u] = want;
+          key4[u] = pack3(cx + dx, cy + dy, cz + dz);
+          slot4[u] = hash64(key4[u]) & m.mask;
+          raw4[u] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, kNone, kNone);
+          if (want) raw4[u] = __ldg(reinterpret_cast<const uint4*>(m.table + slot4[u]));
+        }
+        unsigned hits = 0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          unsigned long long ek = ((unsigned long long)raw4[u].y << 32) | raw4[u].x;
+          while (want4[u] && ek != key4[u] && ek != kEmptyKey) {
+            slot4[u] = (slot4[u] + 1) & m.mask;
+            raw4[u] = __ldg(reinterpret_cast<const uint4*>(m.table + slot4[u]));
+            ek = ((unsigned long long)raw4[u].y << 32) | raw4[u].x;
+          }
+          hits |= g.ballot(want4[u] && ek == key4[u]) << (u * G);
+        }
+        scan_hits<G, 4>(m, g, hits, raw4, qx, qy, qz, max_bits, L);
+      }
+    } else
     for (int idx0 = 0; idx0 < total; idx0 += G) {
       const int idx = idx0 + g.gl;
       const int dz = idx / (side * side) - ring, dy = (idx / side) % side - ring, dx = idx % side - ring;

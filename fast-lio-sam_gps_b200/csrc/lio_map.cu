@@ -23,11 +23,16 @@ __device__ __forceinline__ uint32_t batch_n(uint32_t n_max, const uint32_t* n_de
   return n < n_max ? n : n_max;
 }
 
+// The batch size is only known on the device (map_incremental's lists), so the grid is sized for the largest batch and
+// a small batch would land in the first few blocks.  Consecutive points go to different blocks instead: every SM
+// gets its share of the per-point latency chains (probe, bucket reads, atomics).
+__device__ __forceinline__ uint32_t spread_index() { return threadIdx.x * gridDim.x + blockIdx.x; }
+
 // ---- pass 1: make sure the cell of every batch point exists -----------------------------------
 __global__ void k_cells_ensure(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
                                uint32_t* __restrict__ ent) {
   const uint32_t n = batch_n(n_max, n_dev);
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  for (uint32_t i = spread_index(); i < n; i += gridDim.x * blockDim.x) {
     const float4 p = pts[i];
     const int cx = vox_of(p.x, m.ds) >> m.cell_shift, cy = vox_of(p.y, m.ds) >> m.cell_shift,
               cz = vox_of(p.z, m.ds) >> m.cell_shift;
@@ -103,7 +108,7 @@ __global__ void k_insert_plain(MapView m, const float4* __restrict__ pts, uint32
                                const uint32_t* __restrict__ ent) {
   const uint32_t n = batch_n(n_max, n_dev);
   const uint32_t base = m.ctr->next_id;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  for (uint32_t i = spread_index(); i < n; i += gridDim.x * blockDim.x) {
     const uint32_t ei = ent[i];
     if (ei == kNone) continue;
     const float4 p = pts[i];
@@ -125,7 +130,7 @@ __global__ void k_ds_scan(MapView m, const float4* __restrict__ pts, uint32_t n_
                           uint32_t vox_mask, uint32_t* __restrict__ tslot, unsigned long long* __restrict__ ebest,
                           uint32_t* __restrict__ ecnt) {
   const uint32_t n = batch_n(n_max, n_dev);
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  for (uint32_t i = spread_index(); i < n; i += gridDim.x * blockDim.x) {
     const uint32_t ei = ent[i];
     tslot[i] = kNone;
     if (ei == kNone) continue;
@@ -191,7 +196,7 @@ __global__ void k_ds_commit(MapView m, const float4* __restrict__ pts, uint32_t 
                             const uint32_t* __restrict__ ecnt) {
   const uint32_t n = batch_n(n_max, n_dev);
   const uint32_t base = m.ctr->next_id;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  for (uint32_t i = spread_index(); i < n; i += gridDim.x * blockDim.x) {
     const uint32_t ts = tslot[i];
     if (ts == kNone) continue;
     const float4 p = pts[i];

@@ -3,9 +3,13 @@
 // Reference: h_share_model / map_incremental in third_party/FAST_LIO/src/laserMapping.cpp
 // (absent submodule; behaviour per SURVEY.md §9.1, §9.3; consumer per §9.6).
 #include <algorithm>
+#include <cstddef>
+#include <cstdlib>
 #include <cstring>
 #include "lio_ctx.h"
+#include <cub/device/device_radix_sort.cuh>
 #include "lio_knn.cuh"
+#include "lio_knn_tile.cuh"
 #include "lio_plane.cuh"
 
 namespace lio {
@@ -73,6 +77,107 @@ __global__ void __launch_bounds__(kKnnBlock) k_knn_batch(MapView m, const float4
       }
       nn[(size_t)i * k + g.gl] = p;
       nn_d2[(size_t)i * k + g.gl] = d2;
+    }
+    if (g.gl == 0) nn_cnt[i] = cnt;
+  }
+}
+
+// ---------------------------------------------------------------- K3, tile form (lio_knn_tile.cuh)
+// sort keys: Morton code of the query's map cell at the current state
+template <bool XFORM>
+__global__ void __launch_bounds__(256) k_tile_keys(MapView m, const float4* __restrict__ pts, int n, StateArg st, uint32_t* __restrict__ keys,
+                                                   uint32_t* __restrict__ vals) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 b = __ldg(pts + i);
+    float qx = b.x, qy = b.y, qz = b.z;
+    if (XFORM) body_to_world(st, b.x, b.y, b.z, qx, qy, qz);
+    keys[i] = tile_key(m, qx, qy, qz);
+    vals[i] = (uint32_t)i;
+  }
+}
+
+constexpr int kTileWarps = 4;
+
+// One warp per tile of 32 queries taken in `order` (tiles handed out through an atomic counter); results are scattered
+// back to the queries' own rows.  ctr[0] = tile counter, ctr[1] = leftover count (both zeroed by the previous k_knn_left).
+template <bool XFORM>
+__global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ order,
+                                                               int n, StateArg st, int k, float max_d2, float4* __restrict__ nn,
+                                                               float* __restrict__ nn_d2, int* __restrict__ nn_cnt,
+                                                               uint32_t* __restrict__ ctr, uint32_t* __restrict__ left) {
+  __shared__ TileSmem smem[kTileWarps];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  TileSmem& sm = smem[warp];
+  const int tiles = (n + 31) / 32;
+  const float4 pad = make_float4(0.f, 0.f, 0.f, __uint_as_float(kEmptyId));
+  const float inf = __int_as_float(0x7f800000);
+  while (true) {
+    int tile = 0;
+    if (lane == 0) tile = (int)atomicAdd(ctr, 1u);
+    tile = __shfl_sync(0xFFFFFFFFu, tile, 0);
+    if (tile >= tiles) break;
+    const int t = tile * 32 + lane;
+    const bool valid = t < n;
+    const uint32_t i = valid ? __ldg(order + t) : 0u;
+    float qx = 0.f, qy = 0.f, qz = 0.f;
+    if (valid) {
+      const float4 b = __ldg(pts + i);
+      qx = b.x, qy = b.y, qz = b.z;
+      if (XFORM) body_to_world(st, b.x, b.y, b.z, qx, qy, qz);
+    }
+    const unsigned pending = tile_search(m, sm, lane, qx, qy, qz, valid, max_d2, [&](const Top32& L, int cnt) {
+      cnt = min(cnt, k);
+      const uint32_t ks[kK] = {L.b0, L.b1, L.b2, L.b3, L.b4};
+      const uint32_t rs[kK] = {L.r0, L.r1, L.r2, L.r3, L.r4};
+#pragma unroll
+      for (int j = 0; j < kK; ++j)
+        if (j < k) {
+          const bool have = j < cnt;
+          nn[(size_t)i * k + j] = have ? sm.pts[rs[j]] : pad;
+          if (nn_d2) nn_d2[(size_t)i * k + j] = have ? __uint_as_float(ks[j]) : inf;
+        }
+      nn_cnt[i] = cnt;
+    });
+    if (pending) {  // defer to k_knn_left
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(ctr + 1, (uint32_t)__popc(pending));
+      base = __shfl_sync(0xFFFFFFFFu, base, 0);
+      if ((pending >> lane) & 1u) left[base + __popc(pending & ((1u << lane) - 1u))] = i;
+    }
+  }
+}
+
+// Per-query search (lio_knn.cuh, 8 lanes per query) of the queries the tile kernel deferred.
+template <bool XFORM>
+__global__ void __launch_bounds__(kKnnBlock) k_knn_left(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
+                                                        StateArg st, int k, float max_d2, float4* __restrict__ nn,
+                                                        float* __restrict__ nn_d2, int* __restrict__ nn_cnt, uint32_t* __restrict__ ctr,
+                                                        uint32_t* __restrict__ ctr_next, uint32_t* __restrict__ stats) {
+  const Group<8> g;
+  const int groups_per_block = kKnnBlock / 8;
+  const int gid = blockIdx.x * groups_per_block + (threadIdx.x / 8);
+  const int gstride = gridDim.x * groups_per_block;
+  const int n_left = (int)ctr[1];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    ctr_next[0] = ctr_next[1] = 0u;  // the next search uses the other counter pair
+    if (stats) atomicAdd(stats, (uint32_t)n_left);
+  }
+  const float4 pad = make_float4(0.f, 0.f, 0.f, __uint_as_float(kEmptyId));
+  const float inf = __int_as_float(0x7f800000);
+  for (int j = gid; j < n_left; j += gstride) {
+    const uint32_t i = __ldg(left + j);
+    const float4 b = __ldg(pts + i);
+    float qx = b.x, qy = b.y, qz = b.z;
+    if (XFORM) body_to_world(st, b.x, b.y, b.z, qx, qy, qz);
+    unsigned long long key;
+    uint32_t ref;
+    int cnt;
+    knn_search<8>(m, g, qx, qy, qz, max_d2, key, ref, cnt);
+    cnt = min(cnt, k);
+    if (g.gl < k) {
+      const bool have = g.gl < cnt;
+      nn[(size_t)i * k + g.gl] = have ? __ldg(m.slots + ref) : pad;
+      if (nn_d2) nn_d2[(size_t)i * k + g.gl] = have ? __uint_as_float((uint32_t)(key >> 32)) : inf;
     }
     if (g.gl == 0) nn_cnt[i] = cnt;
   }
@@ -245,39 +350,47 @@ __global__ void __launch_bounds__(kRedBlock) k_plane_reduce(const float4* __rest
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  // last block: sum the block partials in block order, two halves in parallel
-  __shared__ double s_half[2][NV];
-  const int v = threadIdx.x & 127, half = threadIdx.x >> 7;
-  if (v < NV) {
-    const int nb = gridDim.x, mid = (nb + 1) / 2;
-    const int lo = half ? mid : 0, hi = half ? nb : mid;
+  // last block: sum the block partials in a fixed order (8 interleaved chains per value, then a fixed 8-way combine),
+  // assemble the result block in shared memory and ship it to the mapped host block with 16-byte stores
+  __shared__ double s_part[kRedWarps][NV];
+  __shared__ __align__(16) double s_out[160];
+  for (int e = threadIdx.x; e < 160; e += blockDim.x) s_out[e] = 0.0;
+  if (lane < NV) {
+    const int nb = gridDim.x;
     double sum = 0.0;
-    for (int b = lo; b < hi; ++b) sum += __ldcg(partials + (size_t)b * kMaxVals + v);
-    s_half[half][v] = sum;
+    for (int b = warp; b < nb; b += kRedWarps) sum += __ldcg(partials + (size_t)b * kMaxVals + lane);
+    s_part[warp][lane] = sum;
+  }
+  if (NV > 32) {  // 12-column form: values 32..NV-1
+    for (int v = 32 + lane; v < NV; v += 32) {
+      const int nb = gridDim.x;
+      double sum = 0.0;
+      for (int b = warp; b < nb; b += kRedWarps) sum += __ldcg(partials + (size_t)b * kMaxVals + v);
+      s_part[warp][v] = sum;
+    }
   }
   __syncthreads();
   if (threadIdx.x < NV) {
-    const double val = s_half[0][threadIdx.x] + s_half[1][threadIdx.x];
+    double val = 0.0;
+#pragma unroll
+    for (int w = 0; w < kRedWarps; ++w) val += s_part[w][threadIdx.x];
     const int a = s_pa[threadIdx.x], b = s_pb[threadIdx.x];
     if (a < NCOL && b < NCOL) {
-      out->HTH[a * 12 + b] = val;
-      out->HTH[b * 12 + a] = val;
+      s_out[a * 12 + b] = val;
+      s_out[b * 12 + a] = val;
     } else if (b == NCOL) {
-      out->HTz[a] = val;
+      s_out[144 + a] = val;
     } else if (a == NCOL + 1) {
-      out->n_eff = val;
+      s_out[157] = val;  // n_eff
     } else {
-      out->res_sum = val;
+      s_out[156] = val;  // res_sum
     }
   }
-  if (NCOL == 6) {
-    // columns 6..11 are identically zero when extrinsic_est_en is off
-    for (int e = threadIdx.x; e < 144; e += blockDim.x) {
-      const int a = e / 12, b = e % 12;
-      if (a >= 6 || b >= 6) out->HTH[e] = 0.0;
-    }
-    if (threadIdx.x < 6) out->HTz[6 + threadIdx.x] = 0.0;
-  }
+  __syncthreads();
+  static_assert(offsetof(HShareOut, HTz) == 144 * 8 && offsetof(HShareOut, res_sum) == 156 * 8 && offsetof(HShareOut, n_eff) == 157 * 8 &&
+                    offsetof(HShareOut, seq) == 158 * 8,
+                "result block layout");
+  if (threadIdx.x < 79) reinterpret_cast<double2*>(out)[threadIdx.x] = reinterpret_cast<const double2*>(s_out)[threadIdx.x];
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -448,6 +561,13 @@ int scan_alloc(lio_ctx* c) {
   LIO_CUDA(cudaMalloc(&c->blk_cnt, sizeof(uint32_t) * 2 * ((n + 255) / 256 + 1)));
   LIO_CUDA(cudaMalloc(&c->list_add, sizeof(float4) * n));
   LIO_CUDA(cudaMalloc(&c->list_nodown, sizeof(float4) * n));
+  LIO_CUDA(cudaMalloc(&c->tile_stats, sizeof(uint32_t) * 8));  // [0..3] stats, [4..7] two (tile, leftover) counter pairs
+  LIO_CUDA(cudaMemsetAsync(c->tile_stats, 0, sizeof(uint32_t) * 8, c->stream));
+  {
+    const char* e = getenv("LIO_KNN_MODE");
+    c->knn_mode = (e && std::strcmp(e, "group") == 0) ? 0 : 1;
+  }
+  if (int rc = tile_ensure(c, (uint32_t)n)) return rc;
   c->partial_blocks = c->n_sms * 2;
   LIO_CUDA(cudaMalloc(&c->partials, sizeof(double) * kMaxVals * (size_t)c->partial_blocks));
   LIO_CUDA(cudaHostAlloc(&c->out_host, sizeof(HShareOut), cudaHostAllocMapped));
@@ -470,14 +590,82 @@ void scan_free(lio_ctx* c) {
   cudaFree(c->list_add);
   cudaFree(c->list_nodown);
   cudaFree(c->partials);
+  cudaFree(c->tile_stats);
+  cudaFree(c->tile_tmp);
+  for (int j = 0; j < 2; ++j) {
+    cudaFree(c->tile_keys[j]);
+    cudaFree(c->tile_vals[j]);
+  }
   if (c->out_host) cudaFreeHost(c->out_host);
+}
+
+int tile_ensure(lio_ctx* c, uint32_t n) {
+  if (n <= c->tile_cap) return LIO_OK;
+  for (int j = 0; j < 2; ++j) {
+    cudaFree(c->tile_keys[j]);
+    cudaFree(c->tile_vals[j]);
+    c->tile_keys[j] = c->tile_vals[j] = nullptr;
+  }
+  cudaFree(c->tile_tmp);
+  c->tile_tmp = nullptr;
+  c->tile_cap = 0;
+  const uint32_t cap = n + n / 8 + 1024;
+  for (int j = 0; j < 2; ++j) {
+    LIO_CUDA(cudaMalloc(&c->tile_keys[j], sizeof(uint32_t) * cap));
+    LIO_CUDA(cudaMalloc(&c->tile_vals[j], sizeof(uint32_t) * cap));
+  }
+  size_t bytes = 0;
+  LIO_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0], c->tile_vals[1], (int)cap, 0, 30,
+                                           c->stream));
+  LIO_CUDA(cudaMalloc(&c->tile_tmp, bytes));
+  c->tile_tmp_bytes = bytes;
+  c->tile_cap = cap;
+  c->order_valid = false;
+  return LIO_OK;
+}
+
+// Morton order of n query points (body points at `st` when xform) -> c->tile_vals[1]
+static int tile_order(lio_ctx* c, const float4* pts, int n, const StateArg& st, bool xform) {
+  int rc = tile_ensure(c, (uint32_t)n);
+  if (rc) return rc;
+  const int grid = std::max(1, std::min((n + 255) / 256, c->n_sms * 8));
+  if (xform)
+    k_tile_keys<true><<<grid, 256, 0, c->stream>>>(c->map, pts, n, st, c->tile_keys[0], c->tile_vals[0]);
+  else
+    k_tile_keys<false><<<grid, 256, 0, c->stream>>>(c->map, pts, n, st, c->tile_keys[0], c->tile_vals[0]);
+  size_t bytes = c->tile_tmp_bytes;
+  LIO_CUDA(cub::DeviceRadixSort::SortPairs(c->tile_tmp, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0], c->tile_vals[1], n, 0, 30,
+                                           c->stream));
+  c->launches += 1;  // + the library's sort passes (not ours)
+  return LIO_OK;
+}
+
+static int tile_grid(const lio_ctx* c, int n) {
+  const int tiles = (n + 31) / 32;
+  return std::max(1, std::min((tiles + kTileWarps - 1) / kTileWarps, c->n_sms * 8));
 }
 
 int scan_knn(lio_ctx* c, const double* state_host) {
   const int n = c->scan_n;
+  const StateArg st = make_state(state_host);
   timer_begin(c, T_KNN);
-  k_scan_knn<8><<<knn_grid(c, n, 8), kKnnBlock, 0, c->stream>>>(c->map, c->body, n, make_state(state_host), c->cfg.max_sqdist,
-                                                                 c->nn, c->nn_d2, c->nn_cnt);
+  if (c->knn_mode == 1) {
+    if (!c->order_valid) {  // once per scan: later calls move the points by centimetres, the order stays coherent
+      int rc = tile_order(c, c->body, n, st, true);
+      if (rc) return rc;
+      c->order_valid = true;
+    }
+    uint32_t* ctr = c->tile_stats + 4 + 2 * (c->tile_flip & 1);
+    uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
+    c->tile_flip ^= 1;
+    k_knn_tile<true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
+                                                                          c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0]);
+    k_knn_left<true><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn, c->nn_d2,
+                                                                 c->nn_cnt, ctr, ctr_next, c->tile_stats);
+    c->launches += 1;
+  } else {
+    k_scan_knn<8><<<knn_grid(c, n, 8), kKnnBlock, 0, c->stream>>>(c->map, c->body, n, st, c->cfg.max_sqdist, c->nn, c->nn_d2, c->nn_cnt);
+  }
   c->launches += 1;
   timer_end(c);
   LIO_CUDA(cudaGetLastError());
@@ -487,7 +675,24 @@ int scan_knn(lio_ctx* c, const double* state_host) {
 
 int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float4* out_nn, float* out_d2, int* out_cnt) {
   timer_begin(c, T_KNN);
-  k_knn_batch<8><<<knn_grid(c, n, 8), kKnnBlock, 0, c->stream>>>(c->map, q_dev, n, k, max_d2, out_nn, out_d2, out_cnt);
+  if (c->knn_mode == 1) {
+    const bool keep = c->order_valid && (uint32_t)n <= c->tile_cap;  // the scan's order lives in the same buffers
+    StateArg st{};
+    int rc = tile_order(c, q_dev, n, st, false);
+    if (rc) return rc;
+    (void)keep;
+    c->order_valid = false;
+    uint32_t* ctr = c->tile_stats + 4 + 2 * (c->tile_flip & 1);
+    uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
+    c->tile_flip ^= 1;
+    k_knn_tile<false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, q_dev, c->tile_vals[1], n, st, k, max_d2, out_nn, out_d2,
+                                                                           out_cnt, ctr, c->tile_vals[0]);
+    k_knn_left<false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt, ctr,
+                                                                  ctr_next, c->tile_stats);
+    c->launches += 1;
+  } else {
+    k_knn_batch<8><<<knn_grid(c, n, 8), kKnnBlock, 0, c->stream>>>(c->map, q_dev, n, k, max_d2, out_nn, out_d2, out_cnt);
+  }
   c->launches += 1;
   timer_end(c);
   LIO_CUDA(cudaGetLastError());

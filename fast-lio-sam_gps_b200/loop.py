@@ -98,6 +98,13 @@ def _result(r: LoopResult):
                 iterations=r.iterations, state=r.state, n_src=r.n_src, n_dst=r.n_dst)
 
 
+def shard_pairs(n_pairs, rank, world):
+    """Contiguous slice [lo, hi) of the pair list owned by `rank` (sizes differ by at most one)."""
+    base, rem = divmod(n_pairs, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
 class LoopClosure:
     """Mirror of the reference's LoopClosure: keyframes live on the device, candidate pairs are verified in batches.
 

@@ -114,6 +114,8 @@ void lio_boxminus(const double* a, const double* b, double* dx23);
 int lio_timing_enable(lio_ctx* ctx, int on);
 int lio_timing_get(lio_ctx* ctx, const char* name, double* mean_ms, int* launches);
 int lio_timing_reset(lio_ctx* ctx);
+/* queries of all searches so far that left the shared-memory tile path for the per-query fallback search */
+int lio_knn_stats(lio_ctx* ctx, uint64_t* fallback_queries);
 /* number of kernels this context has launched since creation */
 int64_t lio_launch_count(lio_ctx* ctx);
 
