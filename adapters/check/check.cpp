@@ -1,0 +1,50 @@
+// Type-checks the reference-side adapters against stand-in types (see ref_types_mock.hpp) and, when a device is present,
+// runs them once.  Built by `make -C adapters`; linked against the in-tree liblio_b200.so.
+#include <cstdio>
+#include "ref_types_mock.hpp"
+#include "../fastlio_b200.hpp"
+#include "../loop_closure_b200.hpp"
+
+int main() {
+  if (lio_device_count() <= 0) {
+    std::printf("adapters: compiled and linked; no CUDA device, nothing run\n");
+    return 0;
+  }
+  try {
+    FastLioB200 lio(0.5f, 1000.0, 300.0f, false, 1u << 16, 1u << 12);
+    pcl::PointCloud<PointType> world, body;
+    for (int i = 0; i < 40; ++i)
+      for (int j = 0; j < 40; ++j) {
+        PointType p{};
+        p.x = 0.25f * i, p.y = 0.25f * j, p.z = 0.f;
+        world.points.push_back(p);
+        if ((i + j) % 3 == 0) {
+          p.z = 0.01f;
+          body.points.push_back(p);
+        }
+      }
+    lio.build(world);
+    lio.set_scan(body);
+    mock::state_ikfom s;
+    mock::dyn_share_datastruct d;
+    lio.h_share_model(s, d);
+    std::printf("adapters: h_share_model valid=%d rows=%d, map=%d\n", (int)d.valid, d.h_x.r, lio.map_size());
+    lio.map_incremental(s);
+
+    LoopClosureConfig cfg;
+    cfg.num_submap_keyframes_ = 1, cfg.voxel_res_ = 0.3, cfg.loop_detection_radius_ = 35, cfg.loop_detection_timediff_threshold_ = 0.5;
+    cfg.icp_score_threshold_ = 1.5, cfg.icp_max_corr_dist_ = 52.5;
+    LoopClosureB200 lc(cfg);
+    std::vector<PosePcd> kfs(4);
+    for (int k = 0; k < 4; ++k) {
+      kfs[k].pcd_ = world, kfs[k].idx_ = k, kfs[k].timestamp_ = k;
+      kfs[k].pose_corrected_eig_(0, 3) = 0.05 * k;
+    }
+    RegistrationOutput r = lc.performLoopClosure(kfs[2], kfs, 0);
+    std::printf("adapters: loop closure converged=%d valid=%d score=%g\n", (int)r.is_converged_, (int)r.is_valid_, r.score_);
+  } catch (const std::exception &e) {
+    std::printf("adapters: FAILED: %s\n", e.what());
+    return 1;
+  }
+  return 0;
+}

@@ -69,3 +69,31 @@ def test_product_never_touches_the_oracle():
                         if re.search(r"(from|import)\s+oracle|liblio_oracle|orc_[a-z_]+\(", code):
                             bad.append(os.path.join(dp, f))
     assert not bad, bad
+
+
+def _adapter_check():
+    import subprocess
+
+    res = subprocess.run(["make", "-C", os.path.join(ROOT, "adapters")], capture_output=True, text=True)
+    assert res.returncode == 0, res.stdout + res.stderr
+    return subprocess.run([os.path.join(ROOT, "adapters", "check", "adapter_check")], capture_output=True, text=True, timeout=120)
+
+
+def test_adapters_compile_and_link(pkg):
+    """The reference-side C++ adapters type-check against the C-ABI and link with the library."""
+    import torch
+
+    if not os.path.exists(pkg.LIB_PATH):
+        pkg.build_library()
+    out = _adapter_check()
+    assert out.returncode == 0, out.stdout + out.stderr
+    if not torch.cuda.is_available():
+        assert "no CUDA device" in out.stdout
+
+
+@pytest.mark.gpu
+def test_adapters_run_on_device(pkg):
+    """Same binary on the GPU box: FastLioB200::h_share_model fills h_x / h, LoopClosureB200::performLoopClosure converges."""
+    out = _adapter_check()
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "h_share_model valid=1" in out.stdout and "converged=1" in out.stdout, out.stdout
