@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="iekf", choices=["iekf", "loop"])
+    ap.add_argument("--workload", default="iekf", choices=["iekf", "loop", "knn_sweep"])
     ap.add_argument("--scans", type=int, default=4, help="distinct synthetic scans cycled through")
     ap.add_argument("--n-scan", type=int, default=N_SCAN)
     ap.add_argument("--n-map", type=int, default=N_MAP)
@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--pairs", type=int, default=256, help="loop workload: candidate pairs in the batch")
     ap.add_argument("--submap-range", type=int, default=12, help="loop workload: R (2R+1 keyframes per side)")
     ap.add_argument("--n-pass", type=int, default=100, help="loop workload: keyframes per pass of the out-and-back drive")
+    ap.add_argument("--sweep-map", type=int, default=20_000_000, help="knn_sweep workload: map points")
+    ap.add_argument("--sweep-queries", type=int, default=100_000, help="knn_sweep workload: queries per call")
     ap.add_argument("--no-loop", action="store_true", help="iekf workload: skip the loop_icp section of the JSON line")
     return ap.parse_args()
 
@@ -198,7 +200,8 @@ def run_ours(args, synth):
 
     w = make_iekf_workload(synth, args.n_scan, args.n_map, args.scans, rank=rank)
     stream = torch.cuda.Stream()
-    g = pkg.LioContext(0.5, max_points=args.n_map + 8 * args.n_scan, max_scan=args.n_scan, device=local_rank, stream=stream.cuda_stream)
+    g = pkg.LioContext(0.5, max_points=args.n_map + 8 * args.n_scan, max_scan=args.n_scan, max_cells=max(1 << 16, args.n_map // 2), device=local_rank,
+                       stream=stream.cuda_stream)  # ~0.38 occupied 1 m cells per map point in this scene -> table load 0.37
     g.map_build(w["map"])
     P0 = synth.default_cov()
     ns = len(w["scans"])
@@ -321,6 +324,8 @@ def main():
     if args.workload == "loop":
         loop_bench = importlib.import_module("bench_loop")
         return loop_bench.main(args)
+    if args.workload == "knn_sweep":
+        return importlib.import_module("bench_sweep").main(args)
     if args.impl == "reference":
         return run_reference(args, synth)
     return run_ours(args, synth)

@@ -94,6 +94,7 @@ LIO_SYMBOLS = {
     "lio_timing_get": (C.c_int, [C.c_void_p, C.c_char_p, _f64p, _i32p]),
     "lio_timing_reset": (C.c_int, [C.c_void_p]),
     "lio_knn_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "lio_gather_probe": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "lio_launch_count": (C.c_int64, [C.c_void_p]),
 }
 
@@ -294,6 +295,11 @@ class LioContext:
         v = C.c_uint64(0)
         self._check(self.lib.lio_knn_stats(self.h, C.byref(v)))
         return int(v.value)
+
+    def gather_probe(self, table_bytes=320 << 20, reps=5):
+        a, b = C.c_double(0), C.c_double(0)
+        self._check(self.lib.lio_gather_probe(self.h, table_bytes, reps, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def launch_count(self):
         return int(self.lib.lio_launch_count(self.h))

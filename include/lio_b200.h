@@ -116,6 +116,9 @@ int lio_timing_get(lio_ctx* ctx, const char* name, double* mean_ms, int* launche
 int lio_timing_reset(lio_ctx* ctx);
 /* queries of all searches so far that left the shared-memory tile path for the per-query fallback search */
 int lio_knn_stats(lio_ctx* ctx, uint64_t* fallback_queries);
+/* Achievable random-gather bandwidth of the device: random 16-byte loads from a table of `table_bytes` (use >= 320 MB so
+ * it exceeds L2).  *gbps_16B counts the 16 requested bytes per load, *gbps_sector the 32-byte sectors they drag. */
+int lio_gather_probe(lio_ctx* ctx, uint64_t table_bytes, int reps, double* gbps_16B, double* gbps_sector);
 /* number of kernels this context has launched since creation */
 int64_t lio_launch_count(lio_ctx* ctx);
 
