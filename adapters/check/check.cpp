@@ -16,10 +16,10 @@ int main() {
     for (int i = 0; i < 40; ++i)
       for (int j = 0; j < 40; ++j) {
         PointType p{};
-        p.x = 0.25f * i, p.y = 0.25f * j, p.z = 0.f;
+        p.x = 0.25f * i, p.y = 0.25f * j, p.z = 1.f;  // (a plane through the origin has no n.p = -1 form)
         world.points.push_back(p);
         if ((i + j) % 3 == 0) {
-          p.z = 0.01f;
+          p.z = 1.01f;
           body.points.push_back(p);
         }
       }

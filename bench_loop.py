@@ -27,8 +27,10 @@ def make_loop_workload(synth, n_pairs=256, n_pass=100, n_az=1800, submap_range=1
     K = 2 * n_pass
     pairs = []
     lo, hi = n_pass + submap_range, K - 2 - submap_range  # keep both submaps full (the newest keyframe is excluded: size-2)
-    for off in (0, -1, 1, -2, 2):
-        for s in range(hi, lo - 1, -1):
+    offs = (0, -1, 1, -2, 2)
+    n_off = next(k for k in range(1, len(offs) + 1) if k * (hi - lo + 1) >= n_pairs or k == len(offs))
+    for s in range(hi, lo - 1, -1):  # pairs of one query keyframe are adjacent: a rank's slice shares its submaps
+        for off in offs[:n_off]:
             d = (K - 1 - s) + off
             if submap_range <= d < n_pass - submap_range and len(pairs) < n_pairs:
                 pairs.append((s, d))
@@ -196,6 +198,8 @@ def main(args):
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     stream = torch.cuda.Stream()
     out = loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, args.steps, max(1, args.warmup), submap_range=R,

@@ -357,7 +357,22 @@ static int h_share_common(lio_ctx* c, const double* state, int redo_knn, bool wa
   if (redo_knn) rc = scan_knn(c, state);
   if (rc == LIO_OK) rc = scan_plane_reduce(c, state, want_rows);
   if (rc) return rc;
-  LIO_CUDA(cudaStreamSynchronize(c->stream));
+  // The reduction's last block writes the result block to mapped host memory and bumps `seq` last: poll it instead of
+  // paying a stream-synchronise wake-up per IEKF iteration; cudaStreamQuery surfaces a failed launch.
+  {
+    const volatile unsigned long long* seq = &c->out_host->seq;
+    for (unsigned spin = 1; *seq != c->out_seq; ++spin) {
+      if ((spin & 0x3FFu) == 0) {
+        const cudaError_t q = cudaStreamQuery(c->stream);
+        if (q == cudaSuccess) break;  // stream drained: the check below decides
+        if (q != cudaErrorNotReady) LIO_CUDA(q);
+      }
+#if defined(__x86_64__)
+      __builtin_ia32_pause();
+#endif
+    }
+    if (want_rows) LIO_CUDA(cudaStreamSynchronize(c->stream));
+  }
   if (c->out_host->seq != c->out_seq) {
     set_error("measurement kernel did not complete (seq %llu, expected %llu)", c->out_host->seq, c->out_seq);
     return LIO_E_CUDA;

@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(kKnnBlock) k_knn_left(MapView m, const float4*
 // One thread per scan point: plane fit, validity, residual, Jacobian row; then per-warp pair sums in
 // FP64 over rows staged in shared memory, block tree, and a deterministic last-block pass.
 template <int NCOL>
-__global__ void __launch_bounds__(kRedBlock) k_plane_reduce(const float4* __restrict__ body, int n, StateArg st,
+__global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce(const float4* __restrict__ body, int n, StateArg st,
                                                             const float4* __restrict__ nn, const int* __restrict__ nn_cnt,
                                                             float4* __restrict__ world, uint8_t* __restrict__ sel,
                                                             float4* __restrict__ plane, double* __restrict__ rows_out,
@@ -568,7 +568,7 @@ int scan_alloc(lio_ctx* c) {
     c->knn_mode = (e && std::strcmp(e, "group") == 0) ? 0 : 1;
   }
   if (int rc = tile_ensure(c, (uint32_t)n)) return rc;
-  c->partial_blocks = c->n_sms * 2;
+  c->partial_blocks = c->n_sms * 4;
   LIO_CUDA(cudaMalloc(&c->partials, sizeof(double) * kMaxVals * (size_t)c->partial_blocks));
   LIO_CUDA(cudaHostAlloc(&c->out_host, sizeof(HShareOut), cudaHostAllocMapped));
   std::memset(c->out_host, 0, sizeof(HShareOut));
