@@ -227,8 +227,8 @@ def run_ours(args, synth):
             g.scan_upload_ptr(pin_scans[j].data_ptr(), args.n_scan)
         else:
             g.scan_set_device(dev_scans[j].data_ptr(), args.n_scan)
-        s, P, info = g.iekf_update(w["starts"][j], P0, max_iter=MAX_ITER, trace=True)
-        g.map_incremental(s, True, want_counts=False)
+        # update_iterated_dyn_share_modified + map_incremental in one enqueue (lio_iekf_update_map): the device-resident loop
+        s, P, info = g.iekf_update_map(w["starts"][j], P0, True, max_iter=MAX_ITER, trace=True)
         return info
 
     def timed(host, steps, warmup, sample_clocks):
@@ -294,10 +294,12 @@ def run_ours(args, synth):
             "dtype": "f32 search/plane + f64 Jacobian/reduction", "data": "synthetic",
             "config": workload_config(args, w, calls / args.steps),
             "corr_per_s": n_eff * world / (dev_ms * 1e-3),
-            "e2e": {"value": e2e, "unit": "scans/s", "h2d_bytes_per_step": args.n_scan * 12 + 36 * 8,
-                    "d2h_bytes_per_step": int(round(e_calls / args.steps * 160 * 8))},
+            # H2D: the scan (xyz f32) + the IekfIO input block (state, P, limit, R); D2H: state, P and the per-call traces the
+            # device loop writes into the mapped result block
+            "e2e": {"value": e2e, "unit": "scans/s", "h2d_bytes_per_step": args.n_scan * 12 + (36 + 529 + 23 + 2) * 8,
+                    "d2h_bytes_per_step": int(round((36 + 529) * 8 + e_calls / args.steps * (36 * 8 + 8) + 16))},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_scan_knn (body->world + exact k=5 NN)", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "k_knn_tile + k_knn_left (body->world + exact k=5 NN; Morton sort on the first call of a scan)", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": knn_ms, "launches_timed": knn_n,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650"},

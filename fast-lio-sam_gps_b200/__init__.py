@@ -86,6 +86,7 @@ LIO_SYMBOLS = {
     "lio_h_share_rows": (C.c_int, [C.c_void_p, _f64p, C.c_int, _u8p, _f64p, _f64p, _i32p]),
     "lio_scan_get": (C.c_int, [C.c_void_p, _f32p, _u32p, _f32p, _i32p, _u8p, _f32p]),
     "lio_iekf_update": (C.c_int, [C.c_void_p, _f64p, _f64p, C.c_double, C.c_int, _f64p, _f64p, _i32p, _i32p, _i32p]),
+    "lio_iekf_update_map": (C.c_int, [C.c_void_p, _f64p, _f64p, C.c_double, C.c_int, _f64p, C.c_int, _f64p, _i32p, _i32p, _i32p]),
     "lio_map_incremental": (C.c_int, [C.c_void_p, _f64p, C.c_int, _i32p, _i32p]),
     "lio_fov_segment": (C.c_int, [C.c_void_p, _f64p, _f32p, _i32p]),
     "lio_boxplus": (None, [_f64p, _f64p]),
@@ -246,7 +247,9 @@ class LioContext:
                                           _p(out["nn_cnt"], _i32p), _p(out["sel"], _u8p), _p(out["plane"], _f32p)))
         return out
 
-    def iekf_update(self, state, P, R=0.001, max_iter=3, limit=None, trace=False):
+    def iekf_update(self, state, P, R=0.001, max_iter=3, limit=None, trace=False, with_map=None):
+        """esekfom's iterated update; with_map=True/False also runs map_incremental(flg_ekf_inited=with_map... see
+        iekf_update_map) in the same enqueue (lio_iekf_update_map)."""
         state = _f64(state).reshape(STATE_DOUBLES).copy()
         P = _f64(P).reshape(ERR_DOF, ERR_DOF).copy()
         limit = _f64(np.full(ERR_DOF, 0.001) if limit is None else limit)
@@ -254,13 +257,20 @@ class LioContext:
         n_eff = np.zeros(max_iter + 1, np.int32)
         knn = np.zeros(max_iter + 1, np.int32)
         done = C.c_int(0)
-        self._check(self.lib.lio_iekf_update(self.h, _p(state, _f64p), _p(P, _f64p), R, max_iter, _p(limit, _f64p),
-                                             _p(it_states, _f64p) if trace else None, _p(n_eff, _i32p) if trace else None,
-                                             _p(knn, _i32p) if trace else None, C.byref(done)))
+        tr = (_p(it_states, _f64p) if trace else None, _p(n_eff, _i32p) if trace else None, _p(knn, _i32p) if trace else None, C.byref(done))
+        if with_map is None:
+            self._check(self.lib.lio_iekf_update(self.h, _p(state, _f64p), _p(P, _f64p), R, max_iter, _p(limit, _f64p), *tr))
+        else:
+            self._check(self.lib.lio_iekf_update_map(self.h, _p(state, _f64p), _p(P, _f64p), R, max_iter, _p(limit, _f64p),
+                                                     int(with_map), *tr))
         if trace:
             d = done.value
             return state, P, dict(iters=d, states=it_states[:d], n_eff=n_eff[:d], knn=knn[:d])
         return state, P, done.value
+
+    def iekf_update_map(self, state, P, flg_ekf_inited=True, **kw):
+        """The per-scan body of the reference's main loop: iterated update, then map_incremental() at the updated state."""
+        return self.iekf_update(state, P, with_map=bool(flg_ekf_inited), **kw)
 
     def map_incremental(self, state, flg_ekf_inited=True, want_counts=True):
         state = _f64(state).reshape(STATE_DOUBLES)

@@ -1,10 +1,17 @@
-// Host-side manifold algebra of the esekfom mirror (product code; FP64).
+// Manifold algebra of the esekfom mirror (product code; FP64; host and device).
 // Mirrors what IKFoM's MTK provides for state_ikfom = (pos, SO3 rot, SO3 offset_R_L_I, offset_T_L_I,
 // vel, bg, ba, S2 grav): exp/log on SO(3), the A_matrix Jacobian helper and the S2 charts
 // (third_party/FAST_LIO/include/IKFoM_toolkit/mtk — absent submodule; SURVEY.md §9.6, IKFoM paper).
 #pragma once
 #include <cmath>
 #include <cstring>
+
+// the same FP64 code runs in esekf_host.cpp and inside the device-resident IEKF step (lio_iekf.cuh)
+#ifdef __CUDACC__
+#define ESEKF_HD __host__ __device__
+#else
+#define ESEKF_HD
+#endif
 
 namespace esekf {
 
@@ -14,17 +21,17 @@ constexpr double kTiny = 1e-11;
 
 struct Vec3 {
   double v[3];
-  double& operator[](int i) { return v[i]; }
-  double operator[](int i) const { return v[i]; }
+  ESEKF_HD double& operator[](int i) { return v[i]; }
+  ESEKF_HD double operator[](int i) const { return v[i]; }
 };
 struct Mat3 {
   double m[9];  // row-major
-  double& operator()(int r, int c) { return m[3 * r + c]; }
-  double operator()(int r, int c) const { return m[3 * r + c]; }
+  ESEKF_HD double& operator()(int r, int c) { return m[3 * r + c]; }
+  ESEKF_HD double operator()(int r, int c) const { return m[3 * r + c]; }
 };
 
-inline Mat3 eye3() { return Mat3{{1, 0, 0, 0, 1, 0, 0, 0, 1}}; }
-inline Mat3 mul(const Mat3& a, const Mat3& b) {
+ESEKF_HD inline Mat3 eye3() { return Mat3{{1, 0, 0, 0, 1, 0, 0, 0, 1}}; }
+ESEKF_HD inline Mat3 mul(const Mat3& a, const Mat3& b) {
   Mat3 r;
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) {
@@ -34,33 +41,33 @@ inline Mat3 mul(const Mat3& a, const Mat3& b) {
     }
   return r;
 }
-inline Vec3 mul(const Mat3& a, const Vec3& x) {
+ESEKF_HD inline Vec3 mul(const Mat3& a, const Vec3& x) {
   Vec3 r;
   for (int i = 0; i < 3; ++i) r[i] = a(i, 0) * x[0] + a(i, 1) * x[1] + a(i, 2) * x[2];
   return r;
 }
-inline Mat3 transpose(const Mat3& a) {
+ESEKF_HD inline Mat3 transpose(const Mat3& a) {
   Mat3 r;
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) r(j, i) = a(i, j);
   return r;
 }
-inline Mat3 scale(const Mat3& a, double s) {
+ESEKF_HD inline Mat3 scale(const Mat3& a, double s) {
   Mat3 r;
   for (int i = 0; i < 9; ++i) r.m[i] = a.m[i] * s;
   return r;
 }
-inline Mat3 add(const Mat3& a, const Mat3& b) {
+ESEKF_HD inline Mat3 add(const Mat3& a, const Mat3& b) {
   Mat3 r;
   for (int i = 0; i < 9; ++i) r.m[i] = a.m[i] + b.m[i];
   return r;
 }
-inline Mat3 skew(const Vec3& w) { return Mat3{{0, -w[2], w[1], w[2], 0, -w[0], -w[1], w[0], 0}}; }
-inline double dot(const Vec3& a, const Vec3& b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
-inline double norm(const Vec3& a) { return std::sqrt(dot(a, a)); }
+ESEKF_HD inline Mat3 skew(const Vec3& w) { return Mat3{{0, -w[2], w[1], w[2], 0, -w[0], -w[1], w[0], 0}}; }
+ESEKF_HD inline double dot(const Vec3& a, const Vec3& b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+ESEKF_HD inline double norm(const Vec3& a) { return std::sqrt(dot(a, a)); }
 
 // rotation vector -> rotation matrix (Rodrigues)
-inline Mat3 so3_exp(const Vec3& w) {
+ESEKF_HD inline Mat3 so3_exp(const Vec3& w) {
   const double th = norm(w);
   if (th < kTiny) return add(eye3(), skew(w));
   const Vec3 k{{w[0] / th, w[1] / th, w[2] / th}};
@@ -69,7 +76,7 @@ inline Mat3 so3_exp(const Vec3& w) {
 }
 
 // rotation matrix -> rotation vector
-inline Vec3 so3_log(const Mat3& R) {
+ESEKF_HD inline Vec3 so3_log(const Mat3& R) {
   double c = 0.5 * ((R(0, 0) + R(1, 1) + R(2, 2)) - 1.0);
   c = c > 1.0 ? 1.0 : (c < -1.0 ? -1.0 : c);
   const Vec3 v{{R(2, 1) - R(1, 2), R(0, 2) - R(2, 0), R(1, 0) - R(0, 1)}};
@@ -80,7 +87,7 @@ inline Vec3 so3_log(const Mat3& R) {
 }
 
 // MTK::A_matrix
-inline Mat3 a_matrix(const Vec3& v) {
+ESEKF_HD inline Mat3 a_matrix(const Vec3& v) {
   const double sq = dot(v, v), n = std::sqrt(sq);
   if (n < kTiny) return eye3();
   const Mat3 K = skew(v);
@@ -90,11 +97,11 @@ inline Mat3 a_matrix(const Vec3& v) {
 // ---- S2 charts: 3x2 basis Bx, boxplus, boxminus, and the two Jacobian helpers Nx_yy / Mx -----------
 struct Mat32 {
   double m[6];  // 3 rows x 2 cols
-  double& operator()(int r, int c) { return m[2 * r + c]; }
-  double operator()(int r, int c) const { return m[2 * r + c]; }
+  ESEKF_HD double& operator()(int r, int c) { return m[2 * r + c]; }
+  ESEKF_HD double operator()(int r, int c) const { return m[2 * r + c]; }
 };
 
-inline Mat32 s2_basis(const Vec3& g) {
+ESEKF_HD inline Mat32 s2_basis(const Vec3& g) {
   Mat32 B{{0, 0, 0, 0, 0, 0}};
   if (g[2] + kGravLen > kTiny) {
     const double d = kGravLen + g[2];
@@ -111,13 +118,13 @@ inline Mat32 s2_basis(const Vec3& g) {
   return B;
 }
 
-inline Vec3 s2_boxplus(const Vec3& g, const double d[2]) {
+ESEKF_HD inline Vec3 s2_boxplus(const Vec3& g, const double d[2]) {
   const Mat32 B = s2_basis(g);
   const Vec3 bu{{B(0, 0) * d[0] + B(0, 1) * d[1], B(1, 0) * d[0] + B(1, 1) * d[1], B(2, 0) * d[0] + B(2, 1) * d[1]}};
   return mul(so3_exp(bu), g);
 }
 
-inline void s2_boxminus(const Vec3& g, const Vec3& other, double out[2]) {
+ESEKF_HD inline void s2_boxminus(const Vec3& g, const Vec3& other, double out[2]) {
   out[0] = out[1] = 0.0;
   const Vec3 cr = mul(skew(g), other);
   const double v_sin = norm(cr), v_cos = dot(g, other);
@@ -134,7 +141,7 @@ inline void s2_boxminus(const Vec3& g, const Vec3& other, double out[2]) {
 }
 
 // J(2x2) = Nx_yy(g_now) * Mx(g_ref, delta)
-inline void s2_jacobian(const Vec3& g_now, const Vec3& g_ref, const double delta[2], double J[4]) {
+ESEKF_HD inline void s2_jacobian(const Vec3& g_now, const Vec3& g_ref, const double delta[2], double J[4]) {
   // Nx_yy = B(g_now)^T * skew(g_now) / len^2   (2x3)
   const Mat32 Bn = s2_basis(g_now);
   const Mat3 Sn = skew(g_now);

@@ -355,7 +355,7 @@ static int h_share_common(lio_ctx* c, const double* state, int redo_knn, bool wa
   }
   int rc = LIO_OK;
   if (redo_knn) rc = scan_knn(c, state);
-  if (rc == LIO_OK) rc = scan_plane_reduce(c, state, want_rows);
+  if (rc == LIO_OK) rc = scan_plane_reduce(c, state, want_rows, redo_knn != 0);
   if (rc) return rc;
   // The reduction's last block writes the result block to mapped host memory and bumps `seq` last: poll it instead of
   // paying a stream-synchronise wake-up per IEKF iteration; cudaStreamQuery surfaces a failed launch.
@@ -462,15 +462,36 @@ int lio_scan_get(lio_ctx* c, float* world, uint32_t* nn_ids, float* nn_xyz, int*
   return LIO_OK;
 }
 
-int lio_iekf_update(lio_ctx* c, double* state, double* P, double R, int max_iter, const double* limit, double* iter_states,
-                    int* n_eff_trace, int* knn_trace, int* iters_done) {
+static int iekf_common(lio_ctx* c, double* state, double* P, double R, int max_iter, const double* limit, double* iter_states,
+                       int* n_eff_trace, int* knn_trace, int* iters_done, bool with_map, int flg_ekf_inited) {
   int rc = check_ctx(c);
   if (rc) return rc;
   if (!state || !P || !limit || max_iter < 1 || !(R > 0)) {
     set_error("lio_iekf_update: bad arguments");
     return LIO_E_ARG;
   }
-  return iekf_update_host(c, state, P, R, max_iter, limit, iter_states, n_eff_trace, knn_trace, iters_done);
+  if (c->scan_n <= 0) {
+    set_error("no scan uploaded");
+    return LIO_E_STATE;
+  }
+  // default: host loop over lio_h_share (one mapped-memory poll per iteration, ~12 us; measured 0.53 ms/scan on B200).
+  // LIO_IEKF_MODE=device enqueues the whole loop on the device (lio_iekf.cuh: no host round trip, but the 23x23 FP64
+  // algebra then runs in one thread block, ~60 us per iteration -> 0.79 ms/scan): kept as a tested alternative.
+  if (c->iekf_mode == 1 && c->knn_mode == 1 && max_iter + 1 <= kIekfMaxCalls)
+    return iekf_update_device(c, state, P, R, max_iter, limit, iter_states, n_eff_trace, knn_trace, iters_done, with_map, flg_ekf_inited);
+  rc = iekf_update_host(c, state, P, R, max_iter, limit, iter_states, n_eff_trace, knn_trace, iters_done);
+  if (rc || !with_map) return rc;
+  return scan_classify_insert(c, state, flg_ekf_inited);
+}
+
+int lio_iekf_update(lio_ctx* c, double* state, double* P, double R, int max_iter, const double* limit, double* iter_states,
+                    int* n_eff_trace, int* knn_trace, int* iters_done) {
+  return iekf_common(c, state, P, R, max_iter, limit, iter_states, n_eff_trace, knn_trace, iters_done, false, 0);
+}
+
+int lio_iekf_update_map(lio_ctx* c, double* state, double* P, double R, int max_iter, const double* limit, int flg_ekf_inited,
+                        double* iter_states, int* n_eff_trace, int* knn_trace, int* iters_done) {
+  return iekf_common(c, state, P, R, max_iter, limit, iter_states, n_eff_trace, knn_trace, iters_done, true, flg_ekf_inited);
 }
 
 int lio_map_incremental(lio_ctx* c, const double* state, int flg_ekf_inited, int* n_add, int* n_nodown) {

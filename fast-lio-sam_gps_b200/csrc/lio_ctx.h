@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include "../../include/lio_b200.h"
 #include "lio_device.cuh"
+#include "lio_iekf.cuh"
 
 namespace lio {
 
@@ -69,6 +70,7 @@ struct lio_ctx {
   int* nn_cnt = nullptr;    // max_scan
   uint8_t* sel = nullptr;   // max_scan
   float4* plane = nullptr;  // max_scan: a b c pd2
+  float4* pfit = nullptr;   // max_scan: a b c d of the plane fitted at the last search (a = NaN: no valid plane)
   double* rows = nullptr;   // max_scan * 13, allocated on first lio_h_share_rows
   uint8_t* cls = nullptr;   // map_incremental class per point
   uint32_t* blk_cnt = nullptr;  // per-block counts for the ordered compaction (2 x blocks)
@@ -87,6 +89,13 @@ struct lio_ctx {
   double* state_dev = nullptr;  // 36 doubles
   double* partials = nullptr;   // reduction partials
   int partial_blocks = 0;
+
+  // device-resident IEKF loop (lio_iekf.cuh)
+  lio::IekfCtl* iekf_ctl = nullptr;  // device
+  lio::IekfIO* io_host = nullptr;    // pinned + mapped
+  lio::IekfIO* io_dev = nullptr;     // device alias of io_host
+  unsigned long long io_seq = 0;
+  int iekf_mode = 0;                 // 0 host loop over lio_h_share (default: measured faster), 1 device loop (LIO_IEKF_MODE=device)
 
   lio::HShareOut* out_host = nullptr;  // pinned + mapped
   lio::HShareOut* out_dev = nullptr;   // device alias of out_host
@@ -124,9 +133,12 @@ int map_export(lio_ctx* c, std::vector<float4>& out);
 // scan / measurement (lio_scan.cu)
 int scan_alloc(lio_ctx* c);
 void scan_free(lio_ctx* c);
-int scan_knn(lio_ctx* c, const double* state_host);
-int scan_plane_reduce(lio_ctx* c, const double* state_host, bool want_rows);
-int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inited);
+int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop = false);
+int scan_plane_reduce(lio_ctx* c, const double* state_host, bool want_rows, bool refit, bool dev_loop = false, int iter_i = 0,
+                      unsigned long long io_seq = 0);
+int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inited, bool dev_loop = false);
+int iekf_update_device(lio_ctx* c, double* state, double* P, double R, int max_iter, const double* limit, double* iter_states,
+                       int* n_eff_trace, int* knn_trace, int* iters_done, bool with_map, int flg_ekf_inited);
 int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float4* out_nn, float* out_d2, int* out_cnt);
 int tile_ensure(lio_ctx* c, uint32_t n);
 

@@ -11,6 +11,7 @@
 #include "lio_knn.cuh"
 #include "lio_knn_tile.cuh"
 #include "lio_plane.cuh"
+#include "lio_iekf.cuh"
 
 namespace lio {
 
@@ -98,14 +99,30 @@ __global__ void __launch_bounds__(256) k_tile_keys(MapView m, const float4* __re
 
 constexpr int kTileWarps = 4;
 
+// DEV kernels belong to the device-resident IEKF loop (lio_iekf.cuh): the state comes from ctl->x instead of the launch
+// parameters.  Returns the state the block should use (block-wide; contains a barrier when DEV).
+template <bool DEV>
+__device__ __forceinline__ const StateArg& block_state(const StateArg& st_param, const IekfCtl* ctl, StateArg& s_st) {
+  if (DEV) {
+    if (threadIdx.x < 36) s_st.s[threadIdx.x] = ctl->x[threadIdx.x];
+    __syncthreads();
+    return s_st;
+  }
+  return st_param;
+}
+
 // One warp per tile of 32 queries taken in `order` (tiles handed out through an atomic counter); results are scattered
 // back to the queries' own rows.  ctr[0] = tile counter, ctr[1] = leftover count (both zeroed by the previous k_knn_left).
-template <bool XFORM>
+template <bool XFORM, bool DEV>
 __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ order,
-                                                               int n, StateArg st, int k, float max_d2, float4* __restrict__ nn,
+                                                               int n, StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
                                                                float* __restrict__ nn_d2, int* __restrict__ nn_cnt,
-                                                               uint32_t* __restrict__ ctr, uint32_t* __restrict__ left) {
+                                                               uint32_t* __restrict__ ctr, uint32_t* __restrict__ left,
+                                                               const IekfCtl* __restrict__ ctl) {
   __shared__ TileSmem smem[kTileWarps];
+  __shared__ StateArg s_st;
+  if (DEV && (ctl->finished || !ctl->converge)) return;  // cached neighbours are reused (ekfom_data.converge == false)
+  const StateArg& st = block_state<DEV>(st_param, ctl, s_st);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   TileSmem& sm = smem[warp];
   const int tiles = (n + 31) / 32;
@@ -148,20 +165,25 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
 }
 
 // Per-query search (lio_knn.cuh, 8 lanes per query) of the queries the tile kernel deferred.
-template <bool XFORM>
+template <bool XFORM, bool DEV>
 __global__ void __launch_bounds__(kKnnBlock) k_knn_left(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
-                                                        StateArg st, int k, float max_d2, float4* __restrict__ nn,
+                                                        StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
                                                         float* __restrict__ nn_d2, int* __restrict__ nn_cnt, uint32_t* __restrict__ ctr,
-                                                        uint32_t* __restrict__ ctr_next, uint32_t* __restrict__ stats) {
+                                                        uint32_t* __restrict__ ctr_next, uint32_t* __restrict__ stats,
+                                                        const IekfCtl* __restrict__ ctl) {
+  __shared__ StateArg s_st;
   const Group<8> g;
   const int groups_per_block = kKnnBlock / 8;
   const int gid = blockIdx.x * groups_per_block + (threadIdx.x / 8);
   const int gstride = gridDim.x * groups_per_block;
-  const int n_left = (int)ctr[1];
+  const bool skip = DEV && (ctl->finished || !ctl->converge);  // the tile kernel did not run: ctr is still zero
+  const int n_left = skip ? 0 : (int)ctr[1];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     ctr_next[0] = ctr_next[1] = 0u;  // the next search uses the other counter pair
-    if (stats) atomicAdd(stats, (uint32_t)n_left);
+    if (stats && !skip) atomicAdd(stats, (uint32_t)n_left);
   }
+  if (skip) return;
+  const StateArg& st = block_state<DEV>(st_param, ctl, s_st);
   const float4 pad = make_float4(0.f, 0.f, 0.f, __uint_as_float(kEmptyId));
   const float inf = __int_as_float(0x7f800000);
   for (int j = gid; j < n_left; j += gstride) {
@@ -186,20 +208,31 @@ __global__ void __launch_bounds__(kKnnBlock) k_knn_left(MapView m, const float4*
 // ---------------------------------------------------------------- K4 + K5
 // One thread per scan point: plane fit, validity, residual, Jacobian row; then per-warp pair sums in
 // FP64 over rows staged in shared memory, block tree, and a deterministic last-block pass.
-template <int NCOL>
-__global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce(const float4* __restrict__ body, int n, StateArg st,
+template <int NCOL, bool DEV>
+__global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce(const float4* __restrict__ body, int n, StateArg st_param,
                                                             const float4* __restrict__ nn, const int* __restrict__ nn_cnt,
                                                             float4* __restrict__ world, uint8_t* __restrict__ sel,
                                                             float4* __restrict__ plane, double* __restrict__ rows_out,
                                                             double* __restrict__ partials, MapCounters* ctr, HShareOut* out,
-                                                            unsigned long long seq) {
+                                                            unsigned long long seq, IekfCtl* ctl, IekfIO* io, int iter_i,
+                                                            float4* __restrict__ pfit, int refit_param) {
   constexpr int NC = NCOL + 3;                          // row | z | 1 | |pd2|
   constexpr int NV = NCOL * (NCOL + 1) / 2 + NCOL + 2;  // pair sums produced
   constexpr int VPL = (NV + 31) / 32;                   // values per lane
-  __shared__ double s_rows[kRedWarps][32][NC];
+  // the staged rows are dead by the time the last block runs the IEKF algebra (DEV): both live in one buffer
+  constexpr size_t kRowsBytes = sizeof(double) * kRedWarps * 32 * NC;
+  constexpr size_t kRawBytes = (DEV && sizeof(IekfSmem) > kRowsBytes) ? sizeof(IekfSmem) : kRowsBytes;
+  __shared__ __align__(16) unsigned char s_raw[kRawBytes];
+  double (*s_rows)[32][NC] = reinterpret_cast<double (*)[32][NC]>(s_raw);
   __shared__ double s_blk[kRedWarps][NV];
   __shared__ uint8_t s_pa[NV], s_pb[NV];
   __shared__ bool s_last;
+  __shared__ StateArg s_st;
+  if (DEV && ctl->finished) return;
+  // esti_plane depends only on the cached neighbours: it is redone when the search was (ekfom_data.converge), otherwise the
+  // plane of the previous call is reused (bit-identical to refitting the same five points, as the reference does)
+  const bool refit = DEV ? (ctl->converge != 0) : (refit_param != 0);
+  const StateArg& st = block_state<DEV>(st_param, ctl, s_st);
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x < NV) {
@@ -244,17 +277,28 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
       body_to_world(st, b.x, b.y, b.z, wx, wy, wz);
       world[i] = make_float4(wx, wy, wz, 0.f);
       float4 pl = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (nn_cnt[i] >= kK) {
-        float P[kK][3];
+      float pabcd[4];
+      bool fit_ok = false;
+      if (refit) {
+        if (nn_cnt[i] >= kK) {
+          float P[kK][3];
 #pragma unroll
-        for (int k = 0; k < kK; ++k) {
-          const float4 q = __ldg(nn + (size_t)i * kK + k);
-          P[k][0] = q.x;
-          P[k][1] = q.y;
-          P[k][2] = q.z;
+          for (int k = 0; k < kK; ++k) {
+            const float4 q = __ldg(nn + (size_t)i * kK + k);
+            P[k][0] = q.x;
+            P[k][1] = q.y;
+            P[k][2] = q.z;
+          }
+          fit_ok = esti_plane(pabcd, P, 0.1f);
         }
-        float pabcd[4];
-        if (esti_plane(pabcd, P, 0.1f)) {
+        pfit[i] = fit_ok ? make_float4(pabcd[0], pabcd[1], pabcd[2], pabcd[3]) : make_float4(__int_as_float(0x7fc00000), 0.f, 0.f, 0.f);
+      } else {
+        const float4 f = pfit[i];
+        fit_ok = f.x == f.x;  // NaN marks "no valid plane"
+        pabcd[0] = f.x, pabcd[1] = f.y, pabcd[2] = f.z, pabcd[3] = f.w;
+      }
+      {
+        if (fit_ok) {
           float pd2 = pabcd[0] * wx + pabcd[1] * wy;
           pd2 = pd2 + pabcd[2] * wz;
           pd2 = pd2 + pabcd[3];
@@ -390,6 +434,11 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
   static_assert(offsetof(HShareOut, HTz) == 144 * 8 && offsetof(HShareOut, res_sum) == 156 * 8 && offsetof(HShareOut, n_eff) == 157 * 8 &&
                     offsetof(HShareOut, seq) == 158 * 8,
                 "result block layout");
+  if (DEV) {  // device-resident loop: the 23x23 update runs right here, nothing goes to the host before the scan is done
+    if (threadIdx.x == 0) ctr->ticket = 0;
+    iekf_step_block<kRedBlock>(ctl, io, s_out, iter_i, seq, *reinterpret_cast<IekfSmem*>(s_raw));
+    return;
+  }
   if (threadIdx.x < 79) reinterpret_cast<double2*>(out)[threadIdx.x] = reinterpret_cast<const double2*>(s_out)[threadIdx.x];
   __threadfence_system();
   __syncthreads();
@@ -401,12 +450,15 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
 
 // ---------------------------------------------------------------- map_incremental (device side)
 // class per point: 0 skip, 1 PointToAdd, 2 PointNoNeedDownsample; block counts for the ordered compaction
-__global__ void __launch_bounds__(256) k_classify(const float4* __restrict__ body, int n, StateArg st, const float4* __restrict__ nn,
+template <bool DEV>
+__global__ void __launch_bounds__(256) k_classify(const float4* __restrict__ body, int n, StateArg st_param, const float4* __restrict__ nn,
                                                   const int* __restrict__ nn_cnt, int flg_ekf_inited, float fs, MapCounters* ctr,
                                                   float4* __restrict__ world, uint8_t* __restrict__ cls,
-                                                  uint32_t* __restrict__ blk_cnt) {
+                                                  uint32_t* __restrict__ blk_cnt, const IekfCtl* __restrict__ ctl) {
   __shared__ uint32_t s_cnt[2];
+  __shared__ StateArg s_st;
   if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
+  const StateArg& st = block_state<DEV>(st_param, ctl, s_st);
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   int c = 0;
@@ -557,6 +609,7 @@ int scan_alloc(lio_ctx* c) {
   LIO_CUDA(cudaMalloc(&c->nn_cnt, sizeof(int) * n));
   LIO_CUDA(cudaMalloc(&c->sel, n));
   LIO_CUDA(cudaMalloc(&c->plane, sizeof(float4) * n));
+  LIO_CUDA(cudaMalloc(&c->pfit, sizeof(float4) * n));
   LIO_CUDA(cudaMalloc(&c->cls, n));
   LIO_CUDA(cudaMalloc(&c->blk_cnt, sizeof(uint32_t) * 2 * ((n + 255) / 256 + 1)));
   LIO_CUDA(cudaMalloc(&c->list_add, sizeof(float4) * n));
@@ -566,6 +619,8 @@ int scan_alloc(lio_ctx* c) {
   {
     const char* e = getenv("LIO_KNN_MODE");
     c->knn_mode = (e && std::strcmp(e, "group") == 0) ? 0 : 1;
+    e = getenv("LIO_IEKF_MODE");
+    c->iekf_mode = (e && std::strcmp(e, "device") == 0) ? 1 : 0;
   }
   if (int rc = tile_ensure(c, (uint32_t)n)) return rc;
   c->partial_blocks = c->n_sms * 4;
@@ -573,6 +628,11 @@ int scan_alloc(lio_ctx* c) {
   LIO_CUDA(cudaHostAlloc(&c->out_host, sizeof(HShareOut), cudaHostAllocMapped));
   std::memset(c->out_host, 0, sizeof(HShareOut));
   LIO_CUDA(cudaHostGetDevicePointer(&c->out_dev, c->out_host, 0));
+  LIO_CUDA(cudaMalloc(&c->iekf_ctl, sizeof(IekfCtl)));
+  LIO_CUDA(cudaMemsetAsync(c->iekf_ctl, 0, sizeof(IekfCtl), c->stream));
+  LIO_CUDA(cudaHostAlloc(&c->io_host, sizeof(IekfIO), cudaHostAllocMapped));
+  std::memset(c->io_host, 0, sizeof(IekfIO));
+  LIO_CUDA(cudaHostGetDevicePointer(&c->io_dev, c->io_host, 0));
   return LIO_OK;
 }
 
@@ -584,6 +644,7 @@ void scan_free(lio_ctx* c) {
   cudaFree(c->nn_cnt);
   cudaFree(c->sel);
   cudaFree(c->plane);
+  cudaFree(c->pfit);
   cudaFree(c->rows);
   cudaFree(c->cls);
   cudaFree(c->blk_cnt);
@@ -597,6 +658,8 @@ void scan_free(lio_ctx* c) {
     cudaFree(c->tile_vals[j]);
   }
   if (c->out_host) cudaFreeHost(c->out_host);
+  cudaFree(c->iekf_ctl);
+  if (c->io_host) cudaFreeHost(c->io_host);
 }
 
 int tile_ensure(lio_ctx* c, uint32_t n) {
@@ -645,7 +708,7 @@ static int tile_grid(const lio_ctx* c, int n) {
   return std::max(1, std::min((tiles + kTileWarps - 1) / kTileWarps, c->n_sms * 8));
 }
 
-int scan_knn(lio_ctx* c, const double* state_host) {
+int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
   const int n = c->scan_n;
   const StateArg st = make_state(state_host);
   timer_begin(c, T_KNN);
@@ -658,10 +721,17 @@ int scan_knn(lio_ctx* c, const double* state_host) {
     uint32_t* ctr = c->tile_stats + 4 + 2 * (c->tile_flip & 1);
     uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
     c->tile_flip ^= 1;
-    k_knn_tile<true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
-                                                                          c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0]);
-    k_knn_left<true><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn, c->nn_d2,
-                                                                 c->nn_cnt, ctr, ctr_next, c->tile_stats);
+    if (dev_loop) {
+      k_knn_tile<true, true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
+                                                                                  c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], c->iekf_ctl);
+      k_knn_left<true, true><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
+                                                                         c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, c->iekf_ctl);
+    } else {
+      k_knn_tile<true, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
+                                                                                   c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], nullptr);
+      k_knn_left<true, false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
+                                                                          c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, nullptr);
+    }
     c->launches += 1;
   } else {
     k_scan_knn<8><<<knn_grid(c, n, 8), kKnnBlock, 0, c->stream>>>(c->map, c->body, n, st, c->cfg.max_sqdist, c->nn, c->nn_d2, c->nn_cnt);
@@ -685,10 +755,10 @@ int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float
     uint32_t* ctr = c->tile_stats + 4 + 2 * (c->tile_flip & 1);
     uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
     c->tile_flip ^= 1;
-    k_knn_tile<false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, q_dev, c->tile_vals[1], n, st, k, max_d2, out_nn, out_d2,
-                                                                           out_cnt, ctr, c->tile_vals[0]);
-    k_knn_left<false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt, ctr,
-                                                                  ctr_next, c->tile_stats);
+    k_knn_tile<false, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, q_dev, c->tile_vals[1], n, st, k, max_d2, out_nn,
+                                                                                  out_d2, out_cnt, ctr, c->tile_vals[0], nullptr);
+    k_knn_left<false, false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
+                                                                         ctr, ctr_next, c->tile_stats, nullptr);
     c->launches += 1;
   } else {
     k_knn_batch<8><<<knn_grid(c, n, 8), kKnnBlock, 0, c->stream>>>(c->map, q_dev, n, k, max_d2, out_nn, out_d2, out_cnt);
@@ -700,34 +770,51 @@ int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float
 }
 
 // launches K4+K5; the result lands in c->out_host once the stream reaches the end of the kernel
-int scan_plane_reduce(lio_ctx* c, const double* state_host, bool want_rows) {
+int scan_plane_reduce(lio_ctx* c, const double* state_host, bool want_rows, bool refit, bool dev_loop, int iter_i,
+                      unsigned long long io_seq) {
   const int n = c->scan_n;
   if (want_rows && !c->rows) LIO_CUDA(cudaMalloc(&c->rows, sizeof(double) * 13 * (size_t)c->cfg.max_scan));
   const int tiles = (n + 31) / 32;
   const int grid = std::max(1, std::min((tiles + kRedWarps - 1) / kRedWarps, c->partial_blocks));
-  const unsigned long long seq = ++c->out_seq;
   timer_begin(c, T_PLANE);
-  if (c->cfg.extrinsic_est_en)
-    k_plane_reduce<12><<<grid, kRedBlock, 0, c->stream>>>(c->body, n, make_state(state_host), c->nn, c->nn_cnt, c->world, c->sel,
-                                                          c->plane, want_rows ? c->rows : nullptr, c->partials, c->map.ctr,
-                                                          c->out_dev, seq);
-  else
-    k_plane_reduce<6><<<grid, kRedBlock, 0, c->stream>>>(c->body, n, make_state(state_host), c->nn, c->nn_cnt, c->world, c->sel,
-                                                         c->plane, want_rows ? c->rows : nullptr, c->partials, c->map.ctr,
-                                                         c->out_dev, seq);
+  if (dev_loop) {
+    StateArg unused{};
+    if (c->cfg.extrinsic_est_en)
+      k_plane_reduce<12, true><<<grid, kRedBlock, 0, c->stream>>>(c->body, n, unused, c->nn, c->nn_cnt, c->world, c->sel, c->plane, nullptr,
+                                                                  c->partials, c->map.ctr, nullptr, io_seq, c->iekf_ctl, c->io_dev, iter_i, c->pfit, 1);
+    else
+      k_plane_reduce<6, true><<<grid, kRedBlock, 0, c->stream>>>(c->body, n, unused, c->nn, c->nn_cnt, c->world, c->sel, c->plane, nullptr,
+                                                                 c->partials, c->map.ctr, nullptr, io_seq, c->iekf_ctl, c->io_dev, iter_i, c->pfit, 1);
+  } else {
+    const unsigned long long seq = ++c->out_seq;
+    if (c->cfg.extrinsic_est_en)
+      k_plane_reduce<12, false><<<grid, kRedBlock, 0, c->stream>>>(c->body, n, make_state(state_host), c->nn, c->nn_cnt, c->world, c->sel,
+                                                                   c->plane, want_rows ? c->rows : nullptr, c->partials, c->map.ctr,
+                                                                   c->out_dev, seq, nullptr, nullptr, 0, c->pfit, refit ? 1 : 0);
+    else
+      k_plane_reduce<6, false><<<grid, kRedBlock, 0, c->stream>>>(c->body, n, make_state(state_host), c->nn, c->nn_cnt, c->world, c->sel,
+                                                                  c->plane, want_rows ? c->rows : nullptr, c->partials, c->map.ctr,
+                                                                  c->out_dev, seq, nullptr, nullptr, 0, c->pfit, refit ? 1 : 0);
+  }
   c->launches += 1;
   timer_end(c);
   LIO_CUDA(cudaGetLastError());
   return LIO_OK;
 }
 
-int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inited) {
+int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inited, bool dev_loop) {
   const int n = c->scan_n;
   if (n <= 0) return LIO_OK;
   const int blocks = (n + 255) / 256;
   timer_begin(c, T_CLASSIFY);
-  k_classify<<<blocks, 256, 0, c->stream>>>(c->body, n, make_state(state_host), c->nn, c->nn_cnt, flg_ekf_inited,
-                                            c->cfg.filter_size_map, c->map.ctr, c->world, c->cls, c->blk_cnt);
+  if (dev_loop) {
+    StateArg unused{};
+    k_classify<true><<<blocks, 256, 0, c->stream>>>(c->body, n, unused, c->nn, c->nn_cnt, flg_ekf_inited, c->cfg.filter_size_map, c->map.ctr,
+                                                    c->world, c->cls, c->blk_cnt, c->iekf_ctl);
+  } else {
+    k_classify<false><<<blocks, 256, 0, c->stream>>>(c->body, n, make_state(state_host), c->nn, c->nn_cnt, flg_ekf_inited,
+                                                     c->cfg.filter_size_map, c->map.ctr, c->world, c->cls, c->blk_cnt, nullptr);
+  }
   k_scan_blocks<<<1, 1024, 0, c->stream>>>(c->blk_cnt, blocks, c->map.ctr);
   k_scatter_lists<<<blocks, 256, 0, c->stream>>>(c->world, c->cls, n, c->blk_cnt, c->list_add, c->list_nodown);
   c->launches += 3;
@@ -736,6 +823,79 @@ int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inite
   int rc = map_add_device(c, c->list_add, (uint32_t)n, &c->map.ctr->list_add, true);
   if (rc) return rc;
   return map_add_device(c, c->list_nodown, (uint32_t)n, &c->map.ctr->list_nodown, false);
+}
+
+// ---------------------------------------------------------------- device-resident IEKF loop (lio_iekf.cuh)
+namespace {
+__global__ void __launch_bounds__(256) k_iekf_begin(IekfCtl* ctl, const IekfIO* io) {
+  const int tid = threadIdx.x;
+  for (int e = tid; e < 36; e += 256) {
+    const double v = io->state_in[e];
+    ctl->x[e] = v;
+    ctl->x_prop[e] = v;
+  }
+  for (int e = tid; e < kNN; e += 256) ctl->P_prop[e] = io->P_in[e];
+  if (tid < kN) ctl->limit[tid] = io->limit[tid];
+  if (tid == 0) {
+    ctl->R = io->R;
+    ctl->max_iter = io->max_iter;
+    ctl->converge = 1;
+    ctl->t = 0;
+    ctl->done = 0;
+    ctl->finished = 0;
+  }
+}
+}  // namespace
+
+// esekfom::update_iterated_dyn_share_modified (+ map_incremental when with_map) enqueued as one chain of kernels: every
+// model call reads the state the previous call's reduction left in ctl->x; the host waits once, on the mapped result block.
+int iekf_update_device(lio_ctx* c, double* state, double* P_io, double R, int max_iter, const double* limit, double* iter_states,
+                       int* n_eff_trace, int* knn_trace, int* iters_done, bool with_map, int flg_ekf_inited) {
+  IekfIO* io = c->io_host;
+  std::memcpy(io->state_in, state, sizeof(io->state_in));
+  std::memcpy(io->P_in, P_io, sizeof(io->P_in));
+  std::memcpy(io->limit, limit, sizeof(io->limit));
+  io->R = R;
+  io->max_iter = max_iter;
+  const unsigned long long seq = ++c->io_seq;
+  k_iekf_begin<<<1, 256, 0, c->stream>>>(c->iekf_ctl, c->io_dev);
+  c->launches += 1;
+  for (int i = -1; i < max_iter; ++i) {
+    int rc = scan_knn(c, state, true);  // by-value state: only the once-per-scan Morton keys use it (the propagated state)
+    if (rc == LIO_OK) rc = scan_plane_reduce(c, nullptr, false, true, true, i, seq);
+    if (rc) return rc;
+  }
+  if (with_map) {
+    int rc = scan_classify_insert(c, nullptr, flg_ekf_inited, true);
+    if (rc) return rc;
+  }
+  const volatile unsigned long long* pseq = &io->seq;
+  for (unsigned spin = 1; *pseq != seq; ++spin) {
+    if ((spin & 0x3FFu) == 0) {
+      const cudaError_t q = cudaStreamQuery(c->stream);
+      if (q == cudaSuccess) break;
+      if (q != cudaErrorNotReady) LIO_CUDA(q);
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
+  if (*pseq != seq) {
+    set_error("device IEKF loop did not complete (seq %llu, expected %llu)", (unsigned long long)*pseq, seq);
+    return LIO_E_CUDA;
+  }
+  const int done = io->iters_done;
+  if (iters_done) *iters_done = done;
+  if (iter_states) std::memcpy(iter_states, io->iter_states, sizeof(double) * 36 * (size_t)done);
+  if (n_eff_trace) std::memcpy(n_eff_trace, io->n_eff, sizeof(int) * (size_t)done);
+  if (knn_trace) std::memcpy(knn_trace, io->knn, sizeof(int) * (size_t)done);
+  if (io->rc) {
+    set_error("lio_iekf_update: covariance / information matrix is singular");
+    return io->rc;
+  }
+  std::memcpy(state, io->state_out, sizeof(io->state_out));
+  std::memcpy(P_io, io->P_out, sizeof(io->P_out));
+  return LIO_OK;
 }
 
 }  // namespace lio

@@ -96,6 +96,14 @@ int lio_scan_get(lio_ctx* ctx, float* world, uint32_t* nn_ids, float* nn_xyz, in
  * *iters_done = number of measurement-model calls made. */
 int lio_iekf_update(lio_ctx* ctx, double* state, double* P, double R, int max_iter, const double* limit,
                     double* iter_states, int* n_eff_trace, int* knn_trace, int* iters_done);
+/* The per-scan body of the reference's main loop in one call: update_iterated_dyn_share_modified followed
+ * by map_incremental() at the updated state (laserMapping.cpp main loop: `kf.update_iterated_dyn_share_modified(...)`
+ * ... `map_incremental()`; absent submodule).  Everything — the measurement-model calls, the 23x23
+ * update of every iteration and the map update — is enqueued on the device without a host round trip; the
+ * call returns when the updated (state, P) have landed in host memory (the map insert may still be in flight
+ * on the context's stream). */
+int lio_iekf_update_map(lio_ctx* ctx, double* state, double* P, double R, int max_iter, const double* limit,
+                        int flg_ekf_inited, double* iter_states, int* n_eff_trace, int* knn_trace, int* iters_done);
 
 /* map_incremental() at the final state, entirely on the device (classification from the cached
  * neighbours, then Add_Points(PointToAdd,true) and Add_Points(PointNoNeedDownsample,false)).

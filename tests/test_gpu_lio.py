@@ -4,6 +4,8 @@ Bars (BASELINE.json north_star): kNN index sets and plane-validity masks bit-exa
 1e-5 relative; per-iteration state updates within 1e-6 m / 1e-6 rad; trajectory divergence < 1 mm.
 The checker is the CPU oracle on identical seeded inputs.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -147,6 +149,104 @@ def test_iekf_update_parity(pair, synth, small_world):
     assert np.abs(gs - os_).max() < STATE_TOL
     assert np.abs(gP - oP).max() < 1e-9
     assert np.linalg.norm(gs[:3] - w["truth"][:3]) < 0.01
+
+
+def _ctx(pkg, mode, **kw):
+    """A context whose lio_iekf_update runs the device-resident loop ('dev') or the host loop over lio_h_share ('host')."""
+    old = os.environ.get("LIO_IEKF_MODE")
+    os.environ["LIO_IEKF_MODE"] = "host" if mode == "host" else "device"
+    try:
+        return pkg.LioContext(0.5, **kw)
+    finally:
+        if old is None:
+            del os.environ["LIO_IEKF_MODE"]
+        else:
+            os.environ["LIO_IEKF_MODE"] = old
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ext", [False, True])
+def test_device_loop_equals_host_loop(pkg, synth, small_world, ext):
+    """The device-resident IEKF loop (lio_iekf.cuh) and the host loop (esekf_host.cpp) run the same FP64 operations in the
+    same order; only libm (sin/cos/atan2) may differ in the last bits."""
+    w = small_world
+    P0 = synth.default_cov()
+    out = {}
+    for mode in ("dev", "host"):
+        g = _ctx(pkg, mode, max_points=1 << 19, max_scan=1 << 16, extrinsic_est_en=ext)
+        g.map_build(w["map"])
+        g.scan_upload(w["scan"])
+        out[mode] = g.iekf_update(w["start"], P0, trace=True)
+        out[mode + "_scan"] = g.scan_get()
+        g.close()
+    (ds, dP, di), (hs, hP, hi) = out["dev"], out["host"]
+    assert di["iters"] == hi["iters"] and np.array_equal(di["n_eff"], hi["n_eff"]) and np.array_equal(di["knn"], hi["knn"])
+    assert np.abs(di["states"] - hi["states"]).max() < 1e-11
+    assert np.abs(ds - hs).max() < 1e-11 and np.abs(dP - hP).max() < 1e-12
+    for k in ("nn_ids", "sel"):
+        assert np.array_equal(out["dev_scan"][k], out["host_scan"][k])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["host", "dev"])
+def test_iekf_update_map_parity(pkg, orc, synth, small_world, mode):
+    """lio_iekf_update_map = update_iterated_dyn_share_modified + map_incremental in one enqueue: same state, covariance
+    and live map as the oracle's two calls; three scans in a row so the second search runs on the grown map."""
+    w = small_world
+    g = _ctx(pkg, mode, max_points=1 << 19, max_scan=1 << 16)
+    o = orc.OracleLio(0.5)
+    g.map_build(w["map"])
+    o.map_build(w["map"])
+    P0 = synth.default_cov()
+    rng = np.random.default_rng(5)
+    for rnd in range(3):
+        scan = (w["scan"] + rng.normal(0, 0.01, w["scan"].shape)).astype(np.float32)
+        g.scan_upload(scan)
+        o.scan_upload(scan)
+        gs, gP, gi = g.iekf_update_map(w["start"], P0, True, trace=True)
+        os_, oP, oi = o.iekf_update(w["start"], P0, trace=True)
+        o.map_incremental(os_, True)
+        assert gi["iters"] == oi["iters"] and np.array_equal(gi["n_eff"], oi["n_eff"]) and np.array_equal(gi["knn"], oi["knn"])
+        assert np.abs(gi["states"] - oi["states"]).max() < STATE_TOL and np.abs(gP - oP).max() < 1e-9
+        gx, gid = g.map_export()
+        ox, oid = o.map_export()
+        assert g.map_size() == o.map_size()
+        assert np.array_equal(gid, oid) and np.array_equal(gx, ox)
+    g.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["host", "dev"])
+def test_iekf_invalid_rounds_and_errors(pkg, orc, synth, small_world, mode):
+    w = small_world
+    P0 = synth.default_cov()
+    # no effective points at all (scan far away from the map): every round invalid, state and covariance unchanged
+    g = _ctx(pkg, mode, max_points=1 << 19, max_scan=1 << 16)
+    o = orc.OracleLio(0.5)
+    g.map_build(w["map"])
+    o.map_build(w["map"])
+    far = (w["scan"] + np.float32(5000.0)).astype(np.float32)
+    g.scan_upload(far)
+    o.scan_upload(far)
+    gs, gP, gi = g.iekf_update(w["start"], P0, trace=True)
+    os_, oP, oi = o.iekf_update(w["start"], P0, trace=True)
+    assert gi["iters"] == oi["iters"] == 4 and not gi["n_eff"].any()
+    assert np.array_equal(gs, w["start"]) and np.array_equal(gP, P0) and np.array_equal(os_, gs)
+    # a singular covariance is reported, not propagated
+    g.scan_upload(w["scan"])
+    with pytest.raises(pkg.LioError):
+        g.iekf_update(w["start"], np.zeros((23, 23)))
+    # and the context stays usable
+    gs2, _, _ = g.iekf_update(w["start"], P0)
+    o.scan_upload(w["scan"])
+    os2, _, _ = o.iekf_update(w["start"], P0)
+    assert np.abs(gs2 - os2).max() < STATE_TOL
+    # without a scan: call-order error, as on the host path
+    g2 = _ctx(pkg, mode, max_points=1 << 12, max_scan=64)
+    with pytest.raises(pkg.LioError):
+        g2.iekf_update(w["start"], P0)
+    g2.close()
+    g.close()
 
 
 def test_map_add_downsample_parity(pkg, orc):
