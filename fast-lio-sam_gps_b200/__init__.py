@@ -24,6 +24,7 @@ CSRC_DIR = os.path.join(_HERE, "csrc")
 
 LIO_OK = 0
 STATE_DOUBLES = 36
+POSE6D_DOUBLES = 22
 ERR_DOF = 23
 NUM_MATCH = 5
 
@@ -87,6 +88,9 @@ LIO_SYMBOLS = {
     "lio_scan_get": (C.c_int, [C.c_void_p, _f32p, _u32p, _f32p, _i32p, _u8p, _f32p]),
     "lio_iekf_update": (C.c_int, [C.c_void_p, _f64p, _f64p, C.c_double, C.c_int, _f64p, _f64p, _i32p, _i32p, _i32p]),
     "lio_iekf_update_map": (C.c_int, [C.c_void_p, _f64p, _f64p, C.c_double, C.c_int, _f64p, C.c_int, _f64p, _i32p, _i32p, _i32p]),
+    "lio_imu_predict": (C.c_int, [_f64p, _f64p, C.c_double, _f64p, _f64p, _f64p]),
+    "lio_scan_undistort": (C.c_int, [C.c_void_p, _f32p, _f64p, C.c_int, _f64p]),
+    "lio_scan_get_body": (C.c_int, [C.c_void_p, _f32p]),
     "lio_map_incremental": (C.c_int, [C.c_void_p, _f64p, C.c_int, _i32p, _i32p]),
     "lio_fov_segment": (C.c_int, [C.c_void_p, _f64p, _f32p, _i32p]),
     "lio_boxplus": (None, [_f64p, _f64p]),
@@ -268,6 +272,18 @@ class LioContext:
             return state, P, dict(iters=d, states=it_states[:d], n_eff=n_eff[:d], knn=knn[:d])
         return state, P, done.value
 
+    def scan_undistort(self, t_ms, imu_pose, end_state):
+        """UndistortPcl on the uploaded scan, in place (t_ms: per-point curvature; imu_pose: (n_pose, 22) Pose6D rows)."""
+        t_ms = _f32(t_ms).reshape(-1)
+        pose = _f64(imu_pose).reshape(-1, POSE6D_DOUBLES)
+        assert len(t_ms) == self.scan_n
+        self._check(self.lib.lio_scan_undistort(self.h, _p(t_ms, _f32p), _p(pose, _f64p), len(pose), _p(_f64(end_state).reshape(STATE_DOUBLES), _f64p)))
+
+    def scan_body(self):
+        out = np.zeros((self.scan_n, 3), np.float32)
+        self._check(self.lib.lio_scan_get_body(self.h, _p(out, _f32p)))
+        return out
+
     def iekf_update_map(self, state, P, flg_ekf_inited=True, **kw):
         """The per-scan body of the reference's main loop: iterated update, then map_incremental() at the updated state."""
         return self.iekf_update(state, P, with_map=bool(flg_ekf_inited), **kw)
@@ -313,6 +329,18 @@ class LioContext:
 
     def launch_count(self):
         return int(self.lib.lio_launch_count(self.h))
+
+
+def imu_predict(state, P, dt, acc, gyro, Q):
+    """esekfom::predict on the host (lio_imu_predict); returns (state, P)."""
+    lib = load_library()
+    state = _f64(state).reshape(STATE_DOUBLES).copy()
+    P = _f64(P).reshape(ERR_DOF, ERR_DOF).copy()
+    rc = lib.lio_imu_predict(_p(state, _f64p), _p(P, _f64p), float(dt), _p(_f64(acc).reshape(3), _f64p), _p(_f64(gyro).reshape(3), _f64p),
+                             _p(_f64(Q).reshape(12, 12), _f64p))
+    if rc != LIO_OK:
+        raise LioError(f"lio_imu_predict: {rc}")
+    return state, P
 
 
 def identity_state(pos=(0, 0, 0), rot=None, grav=(0.19614, -0.14711, -9.80593)):

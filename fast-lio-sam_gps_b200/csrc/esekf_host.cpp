@@ -145,4 +145,84 @@ void lio_boxplus(double* state, const double* dx23) {
 
 void lio_boxminus(const double* a, const double* b, double* dx23) { state_boxminus(load(a), load(b), dx23); }
 
+// esekfom::predict(dt, Q, in) with FAST-LIO's process model (use-ikfom.hpp get_f / df_dx / df_dw; absent submodule,
+// SURVEY.md §8(f)-1).  The Jacobians are sparse: F_x1 = I + dt*f_x differs from the identity only in the blocks written
+// below, and G = dt*f_w has four 3x3 blocks, so they are filled in place instead of going through the flat 24-row form.
+int lio_imu_predict(double* state, double* P, double dt, const double* acc, const double* gyro, const double* Q) {
+  if (!state || !P || !acc || !gyro || !Q) return LIO_E_ARG;
+  State x = load(state);
+  const Vec3 omega{{gyro[0] - x.bg[0], gyro[1] - x.bg[1], gyro[2] - x.bg[2]}};
+  const Vec3 a_b{{acc[0] - x.ba[0], acc[1] - x.ba[1], acc[2] - x.ba[2]}};
+  const Vec3 Ra = mul(x.rot, a_b);
+  const Vec3 a_w{{Ra[0] + x.grav[0], Ra[1] + x.grav[1], Ra[2] + x.grav[2]}};
+  const Mat3 R0 = x.rot;
+  double F[kDof * kDof], G[kDof * 12];
+  std::memset(F, 0, sizeof(F));
+  std::memset(G, 0, sizeof(G));
+  for (int i = 0; i < kDof; ++i) F[i * kDof + i] = 1.0;
+  // rotation rows: Exp(-omega dt) on the diagonal, A(-omega dt) in front of d(omega)/d(bg) = -I and of the gyro noise
+  const Vec3 seg{{omega[0] * -dt, omega[1] * -dt, omega[2] * -dt}};
+  const Mat3 E = so3_exp(seg), A = a_matrix(seg);
+  const Mat3 RhatA = mul(R0, skew(a_b));
+  // gravity chart: Mx(g, 0) = -[g]x B(g)
+  const Mat32 B = s2_basis(x.grav);
+  const Mat3 Sg = skew(x.grav);
+  double Mx[6];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 2; ++c) {
+      double s = 0;
+      for (int k = 0; k < 3; ++k) s += Sg(r, k) * B(k, c);
+      Mx[2 * r + c] = -s;
+    }
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) {
+      F[(3 + r) * kDof + 3 + c] = E(r, c);
+      F[(3 + r) * kDof + 15 + c] = (A(r, c) * -1.0) * dt;
+      F[(12 + r) * kDof + 3 + c] = (RhatA(r, c) * -1.0) * dt;
+      F[(12 + r) * kDof + 18 + c] = (R0(r, c) * -1.0) * dt;
+      G[(3 + r) * 12 + c] = (A(r, c) * -1.0) * dt;
+      G[(12 + r) * 12 + 3 + c] = (R0(r, c) * -1.0) * dt;
+    }
+  for (int r = 0; r < 3; ++r) {
+    F[r * kDof + 12 + r] = dt;  // d(pos)/d(vel)
+    G[(15 + r) * 12 + 6 + r] = dt;
+    G[(18 + r) * 12 + 9 + r] = dt;
+    for (int c = 0; c < 2; ++c) F[(12 + r) * kDof + 21 + c] = Mx[2 * r + c] * dt;
+  }
+  {
+    const double zero[2] = {0.0, 0.0};
+    double J[4];
+    s2_jacobian(x.grav, x.grav, zero, J);  // Nx(g) * Mx(g, 0)
+    F[21 * kDof + 21] = J[0], F[21 * kDof + 22] = J[1], F[22 * kDof + 21] = J[2], F[22 * kDof + 22] = J[3];
+  }
+  // x <- x [+] f dt
+  for (int i = 0; i < 3; ++i) x.pos[i] += x.vel[i] * dt;
+  x.rot = mul(x.rot, so3_exp(Vec3{{omega[0] * dt, omega[1] * dt, omega[2] * dt}}));
+  for (int i = 0; i < 3; ++i) x.vel[i] += a_w[i] * dt;
+  // P <- F P F^T + G Q G^T
+  double T[kDof * kDof], T2[kDof * 12], Pn[kDof * kDof];
+  for (int r = 0; r < kDof; ++r)
+    for (int c = 0; c < kDof; ++c) {
+      double s = 0;
+      for (int k = 0; k < kDof; ++k) s += F[r * kDof + k] * P[k * kDof + c];
+      T[r * kDof + c] = s;
+    }
+  for (int r = 0; r < kDof; ++r)
+    for (int c = 0; c < 12; ++c) {
+      double s = 0;
+      for (int k = 0; k < 12; ++k) s += G[r * 12 + k] * Q[k * 12 + c];
+      T2[r * 12 + c] = s;
+    }
+  for (int r = 0; r < kDof; ++r)
+    for (int c = 0; c < kDof; ++c) {
+      double s = 0, q = 0;
+      for (int k = 0; k < kDof; ++k) s += T[r * kDof + k] * F[c * kDof + k];
+      for (int k = 0; k < 12; ++k) q += T2[r * 12 + k] * G[c * 12 + k];
+      Pn[r * kDof + c] = s + q;
+    }
+  std::memcpy(P, Pn, sizeof(Pn));
+  store(x, state);
+  return LIO_OK;
+}
+
 }  // extern "C"

@@ -340,6 +340,38 @@ int lio_scan_set_device(lio_ctx* c, const void* body_xyzw_dev, int n) {
   return LIO_OK;
 }
 
+int lio_scan_undistort(lio_ctx* c, const float* t_ms, const double* imu_pose, int n_pose, const double* end_state) {
+  int rc = check_ctx(c);
+  if (rc) return rc;
+  if (!t_ms || !imu_pose || !end_state) {
+    set_error("lio_scan_undistort: null argument");
+    return LIO_E_ARG;
+  }
+  if (c->scan_n <= 0) {
+    set_error("no scan uploaded");
+    return LIO_E_STATE;
+  }
+  c->nn_valid = false;
+  c->order_valid = false;
+  return scan_undistort(c, t_ms, imu_pose, n_pose, end_state);
+}
+
+int lio_scan_get_body(lio_ctx* c, float* body_xyz) {
+  int rc = check_ctx(c);
+  if (rc) return rc;
+  const int n = c->scan_n;
+  if (n <= 0 || !body_xyz) return LIO_OK;
+  std::vector<float4> b((size_t)n);
+  LIO_CUDA(cudaMemcpyAsync(b.data(), c->body, sizeof(float4) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  LIO_CUDA(cudaStreamSynchronize(c->stream));
+  for (int i = 0; i < n; ++i) {
+    body_xyz[3 * i] = b[i].x;
+    body_xyz[3 * i + 1] = b[i].y;
+    body_xyz[3 * i + 2] = b[i].z;
+  }
+  return LIO_OK;
+}
+
 static int h_share_common(lio_ctx* c, const double* state, int redo_knn, bool want_rows) {
   if (!state) {
     set_error("null state");

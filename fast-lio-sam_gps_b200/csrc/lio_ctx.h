@@ -65,6 +65,8 @@ struct lio_ctx {
   bool nn_valid = false;
   float4* body = nullptr;   // max_scan
   float4* world = nullptr;  // max_scan (w = unused)
+  float* scan_t = nullptr;    // max_scan: per-point time offsets (ms), allocated on first lio_scan_undistort
+  double* imu_pose = nullptr; // IMU poses of the scan (22 doubles each)
   float4* nn = nullptr;     // max_scan * 5 (xyz, id bits)
   float* nn_d2 = nullptr;   // max_scan * 5
   int* nn_cnt = nullptr;    // max_scan
@@ -139,6 +141,7 @@ int scan_plane_reduce(lio_ctx* c, const double* state_host, bool want_rows, bool
 int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inited, bool dev_loop = false);
 int iekf_update_device(lio_ctx* c, double* state, double* P, double R, int max_iter, const double* limit, double* iter_states,
                        int* n_eff_trace, int* knn_trace, int* iters_done, bool with_map, int flg_ekf_inited);
+int scan_undistort(lio_ctx* c, const float* t_ms_host, const double* pose_host, int n_pose, const double* end_state);
 int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float4* out_nn, float* out_d2, int* out_cnt);
 int tile_ensure(lio_ctx* c, uint32_t n);
 

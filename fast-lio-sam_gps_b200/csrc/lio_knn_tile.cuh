@@ -67,18 +67,19 @@ struct Top32 {
   }
 };
 
-// 10 bits per axis Morton code of a cell (wraps every 1024 cells: locality is all that matters)
-__device__ __forceinline__ uint32_t spread10(uint32_t x) {
-  x &= 0x3ffu;
-  x = (x | (x << 16)) & 0x030000ffu;
-  x = (x | (x << 8)) & 0x0300f00fu;
-  x = (x | (x << 4)) & 0x030c30c3u;
-  x = (x | (x << 2)) & 0x09249249u;
+// 8 bits per axis Morton code of a cell (wraps every 256 cells: locality is all that matters, and 24 key bits are three
+// radix passes instead of four)
+constexpr int kTileKeyBits = 24;
+__device__ __forceinline__ uint32_t spread8(uint32_t x) {
+  x &= 0xffu;
+  x = (x | (x << 8)) & 0x0000f00fu;
+  x = (x | (x << 4)) & 0x000c30c3u;
+  x = (x | (x << 2)) & 0x00249249u;
   return x;
 }
 __device__ __forceinline__ uint32_t tile_key(const MapView& m, float x, float y, float z) {
   const int cx = vox_of(x, m.ds) >> m.cell_shift, cy = vox_of(y, m.ds) >> m.cell_shift, cz = vox_of(z, m.ds) >> m.cell_shift;
-  return spread10((uint32_t)cx) | (spread10((uint32_t)cy) << 1) | (spread10((uint32_t)cz) << 2);
+  return spread8((uint32_t)cx) | (spread8((uint32_t)cy) << 1) | (spread8((uint32_t)cz) << 2);
 }
 
 // Stages every live point of cells [lo, hi] (inclusive cell coordinates).  Returns the number of staged points, or -1

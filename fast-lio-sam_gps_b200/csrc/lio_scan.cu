@@ -574,6 +574,57 @@ __global__ void __launch_bounds__(256) k_scatter_lists(const float4* __restrict_
   (t ? list_nodown : list_add)[off] = world[i];
 }
 
+// ---------------------------------------------------------------- UndistortPcl (the step in front of the path)
+// Backward motion compensation of ImuProcess::UndistortPcl (IMU_Processing.hpp, absent submodule): every point is
+// re-expressed in the LiDAR frame at the scan end from the IMU pose that precedes its own timestamp.  The reference
+// walks the time-sorted cloud backwards with two pointers; here each thread finds its pose by bisection (same segment:
+// the last pose whose offset_time is strictly below the point's time; points at or before pose[0] stay untouched).
+constexpr int kMaxImuPoses = 512;
+__global__ void __launch_bounds__(256) k_undistort(float4* __restrict__ body, const float* __restrict__ t_ms, int n,
+                                                   const double* __restrict__ pose, int n_pose, StateArg end) {
+  using namespace esekf;
+  __shared__ double s_off[kMaxImuPoses];
+  for (int k = threadIdx.x; k < n_pose; k += blockDim.x) s_off[k] = pose[22 * k];
+  __syncthreads();
+  const State e = load(end.s);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double t = (double)t_ms[i] / double(1000);
+    if (!(t > s_off[0])) continue;
+    int lo = 0, hi = n_pose - 2;  // largest head index with offset < t
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_off[mid] < t) lo = mid;
+      else hi = mid - 1;
+    }
+    const double* head = pose + 22 * lo;
+    const double* tail = head + 22;
+    const double dt = t - head[0];
+    Mat3 R_imu;
+    for (int k = 0; k < 9; ++k) R_imu.m[k] = head[13 + k];
+    const Vec3 gyr{{tail[4], tail[5], tail[6]}};
+    Mat3 Ex = eye3();
+    const double wn = norm(gyr);
+    if (wn > 1e-7) {
+      const Mat3 K = skew(Vec3{{gyr[0] / wn, gyr[1] / wn, gyr[2] / wn}});
+      const double ang = wn * dt;
+      Ex = add(add(eye3(), scale(K, sin(ang))), scale(mul(K, K), 1.0 - cos(ang)));
+    }
+    const Mat3 R_i = mul(R_imu, Ex);
+    const float4 b = body[i];
+    const Vec3 P_i{{(double)b.x, (double)b.y, (double)b.z}};
+    Vec3 T_ei;
+    for (int k = 0; k < 3; ++k) T_ei[k] = ((head[10 + k] + head[7 + k] * dt) + ((tail[1 + k] * 0.5) * dt) * dt) - e.pos[k];
+    Vec3 p = mul(e.offR, P_i);
+    for (int k = 0; k < 3; ++k) p[k] += e.offT[k];
+    p = mul(R_i, p);
+    for (int k = 0; k < 3; ++k) p[k] += T_ei[k];
+    p = mul(transpose(e.rot), p);
+    for (int k = 0; k < 3; ++k) p[k] -= e.offT[k];
+    p = mul(transpose(e.offR), p);
+    body[i] = make_float4((float)p[0], (float)p[1], (float)p[2], b.w);
+  }
+}
+
 __global__ void k_expand_xyz(const float* __restrict__ xyz, int n, float4* __restrict__ out) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     out[i] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], 0.f);
@@ -659,7 +710,27 @@ void scan_free(lio_ctx* c) {
   }
   if (c->out_host) cudaFreeHost(c->out_host);
   cudaFree(c->iekf_ctl);
+  cudaFree(c->scan_t);
+  cudaFree(c->imu_pose);
   if (c->io_host) cudaFreeHost(c->io_host);
+}
+
+int scan_undistort(lio_ctx* c, const float* t_ms_host, const double* pose_host, int n_pose, const double* end_state) {
+  const int n = c->scan_n;
+  if (n_pose < 2 || n_pose > kMaxImuPoses) {
+    set_error("lio_scan_undistort: need 2..%d IMU poses (got %d)", kMaxImuPoses, n_pose);
+    return LIO_E_ARG;
+  }
+  if (!c->scan_t) LIO_CUDA(cudaMalloc(&c->scan_t, sizeof(float) * (size_t)c->cfg.max_scan));
+  if (!c->imu_pose) LIO_CUDA(cudaMalloc(&c->imu_pose, sizeof(double) * 22 * kMaxImuPoses));
+  LIO_CUDA(cudaMemcpyAsync(c->scan_t, t_ms_host, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  LIO_CUDA(cudaMemcpyAsync(c->imu_pose, pose_host, sizeof(double) * 22 * (size_t)n_pose, cudaMemcpyHostToDevice, c->stream));
+  const int grid = std::max(1, std::min((n + 255) / 256, c->n_sms * 8));
+  k_undistort<<<grid, 256, 0, c->stream>>>(c->body, c->scan_t, n, c->imu_pose, n_pose, make_state(end_state));
+  c->launches += 1;
+  LIO_CUDA(cudaGetLastError());
+  LIO_CUDA(cudaStreamSynchronize(c->stream));  // the host buffers may be reused on return
+  return LIO_OK;
 }
 
 int tile_ensure(lio_ctx* c, uint32_t n) {
@@ -678,7 +749,7 @@ int tile_ensure(lio_ctx* c, uint32_t n) {
     LIO_CUDA(cudaMalloc(&c->tile_vals[j], sizeof(uint32_t) * cap));
   }
   size_t bytes = 0;
-  LIO_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0], c->tile_vals[1], (int)cap, 0, 30,
+  LIO_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0], c->tile_vals[1], (int)cap, 0, kTileKeyBits,
                                            c->stream));
   LIO_CUDA(cudaMalloc(&c->tile_tmp, bytes));
   c->tile_tmp_bytes = bytes;
@@ -697,7 +768,7 @@ static int tile_order(lio_ctx* c, const float4* pts, int n, const StateArg& st, 
   else
     k_tile_keys<false><<<grid, 256, 0, c->stream>>>(c->map, pts, n, st, c->tile_keys[0], c->tile_vals[0]);
   size_t bytes = c->tile_tmp_bytes;
-  LIO_CUDA(cub::DeviceRadixSort::SortPairs(c->tile_tmp, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0], c->tile_vals[1], n, 0, 30,
+  LIO_CUDA(cub::DeviceRadixSort::SortPairs(c->tile_tmp, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0], c->tile_vals[1], n, 0, kTileKeyBits,
                                            c->stream));
   c->launches += 1;  // + the library's sort passes (not ours)
   return LIO_OK;

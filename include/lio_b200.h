@@ -105,6 +105,20 @@ int lio_iekf_update(lio_ctx* ctx, double* state, double* P, double R, int max_it
 int lio_iekf_update_map(lio_ctx* ctx, double* state, double* P, double R, int max_iter, const double* limit,
                         int flg_ekf_inited, double* iter_states, int* n_eff_trace, int* knn_trace, int* iters_done);
 
+/* ---- the step in front of the path: IMU forward propagation + per-point undistortion ---------- */
+/* esekfom::predict(dt, Q, in) with FAST-LIO's process model (IKFoM_toolkit/esekfom/esekfom.hpp predict();
+ * include/use-ikfom.hpp get_f / df_dx / df_dw — absent submodule).  HOST FP64 (23x23, serial, ~20 calls per scan):
+ * state in/out LIO_STATE_DOUBLES, P in/out 23x23 row-major, acc/gyro = averaged IMU sample, Q = 12x12 row-major process
+ * noise over (gyro, acc, gyro-bias, acc-bias).  No device work. */
+int lio_imu_predict(double* state, double* P, double dt, const double* acc, const double* gyro, const double* Q);
+#define LIO_POSE6D_DOUBLES 22 /* Pose6D: offset_time [s] | acc3 | gyr3 | vel3 | pos3 | rot 3x3 row-major */
+/* ImuProcess::UndistortPcl's backward compensation (src/IMU_Processing.hpp) applied IN PLACE to the uploaded scan:
+ * t_ms[n] = per-point `curvature` (milliseconds from the scan start, HOST); imu_pose = n_pose x LIO_POSE6D_DOUBLES (HOST,
+ * offset_time ascending, first entry at 0); end_state = state at the scan end.  Invalidates cached neighbours. */
+int lio_scan_undistort(lio_ctx* ctx, const float* t_ms, const double* imu_pose, int n_pose, const double* end_state);
+/* The scan as it currently sits on the device (after upload / undistortion): body_xyz[n*3] (HOST). */
+int lio_scan_get_body(lio_ctx* ctx, float* body_xyz);
+
 /* map_incremental() at the final state, entirely on the device (classification from the cached
  * neighbours, then Add_Points(PointToAdd,true) and Add_Points(PointNoNeedDownsample,false)).
  * Counts are optional; asking for them synchronises. */

@@ -66,6 +66,10 @@ def lib():
         L.orc_fov_segment.argtypes = [C.c_void_p, _f64p, _f32p]
         L.orc_boxplus.argtypes = [_f64p, _f64p]
         L.orc_boxminus.argtypes = [_f64p, _f64p, _f64p]
+        L.orc_imu_predict.restype = None
+        L.orc_imu_predict.argtypes = [_f64p, _f64p, C.c_double, _f64p, _f64p, _f64p]
+        L.orc_undistort.restype = None
+        L.orc_undistort.argtypes = [_f32p, _f32p, C.c_int, _f64p, C.c_int, _f64p]
         # loop closure
         L.orc_loop_create.restype = C.c_void_p
         L.orc_loop_create.argtypes = [C.c_double, C.c_double, C.c_double, C.c_int, C.c_int]
@@ -221,6 +225,24 @@ def boxplus(state, dx):
     d = _f64(dx).reshape(23)
     lib().orc_boxplus(_p(s, _f64p), _p(d, _f64p))
     return s
+
+
+def imu_predict(state, P, dt, acc, gyro, Q):
+    """esekfom::predict restatement (orc_imu.cpp); returns (state, P)."""
+    s = _f64(state).reshape(36).copy()
+    P = _f64(P).reshape(23, 23).copy()
+    lib().orc_imu_predict(_p(s, _f64p), _p(P, _f64p), float(dt), _p(_f64(acc).reshape(3), _f64p), _p(_f64(gyro).reshape(3), _f64p),
+                          _p(_f64(Q).reshape(12, 12), _f64p))
+    return s, P
+
+
+def undistort(xyz, t_ms, imu_pose, end_state):
+    """UndistortPcl's backward sweep (orc_imu.cpp) on a time-sorted cloud; returns the compensated copy."""
+    out = _f32(xyz).reshape(-1, 3).copy()
+    t = _f32(t_ms).reshape(-1)
+    pose = _f64(imu_pose).reshape(-1, 22)
+    lib().orc_undistort(_p(out, _f32p), _p(t, _f32p), len(out), _p(pose, _f64p), len(pose), _p(_f64(end_state).reshape(36), _f64p))
+    return out
 
 
 def boxminus(a, b):
