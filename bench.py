@@ -263,7 +263,11 @@ def run_ours(args, synth):
         g.timing(False)
         return total_ms, calls, n_eff, launches, kt, clocks
 
+    st0 = g.knn_stats_detail()
     dev_ms, calls, n_eff, launches, kt, clocks = timed(False, args.steps, args.warmup, True)
+    st1 = g.knn_stats_detail()
+    knn_calls = max(1, kt["knn"][1]) * (args.warmup + args.steps) / max(1, args.steps)  # the counters also saw the warm-up
+    knn_deferred = {k: (st1[k] - st0[k]) / knn_calls / args.n_scan for k in st0}  # fraction of a scan's queries, per search
     e2e_ms, e_calls, _, _, _, _ = timed(True, args.steps, max(3, args.warmup), False)
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -306,6 +310,7 @@ def run_ours(args, synth):
                          "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": knn_ms, "launches_timed": knn_n,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650"},
             "kernel_ms": {k: {"mean_ms": v[0], "launches": v[1]} for k, v in kt.items()},
+            "knn_deferred_fraction": knn_deferred,
             "clocks": clocks,
         }
         if not args.no_cpu_baseline and world == 1:

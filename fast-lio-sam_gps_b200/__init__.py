@@ -99,6 +99,7 @@ LIO_SYMBOLS = {
     "lio_timing_get": (C.c_int, [C.c_void_p, C.c_char_p, _f64p, _i32p]),
     "lio_timing_reset": (C.c_int, [C.c_void_p]),
     "lio_knn_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "lio_knn_stats_detail": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "lio_gather_probe": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "lio_launch_count": (C.c_int64, [C.c_void_p]),
 }
@@ -321,6 +322,11 @@ class LioContext:
         v = C.c_uint64(0)
         self._check(self.lib.lio_knn_stats(self.h, C.byref(v)))
         return int(v.value)
+
+    def knn_stats_detail(self):
+        v = (C.c_uint64 * 4)()
+        self._check(self.lib.lio_knn_stats_detail(self.h, v))
+        return dict(per_query=int(v[0]), overflow=int(v[1]), incoherent=int(v[2]))
 
     def gather_probe(self, table_bytes=320 << 20, reps=5):
         a, b = C.c_double(0), C.c_double(0)

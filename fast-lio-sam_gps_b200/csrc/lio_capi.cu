@@ -657,6 +657,17 @@ int lio_knn_stats(lio_ctx* c, uint64_t* fallback_queries) {
   return LIO_OK;
 }
 
+int lio_knn_stats_detail(lio_ctx* c, uint64_t* out4) {
+  int rc = check_ctx(c);
+  if (rc) return rc;
+  uint32_t v[4] = {0, 0, 0, 0};
+  LIO_CUDA(cudaMemcpyAsync(v, c->tile_stats, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+  LIO_CUDA(cudaStreamSynchronize(c->stream));
+  if (out4)
+    for (int i = 0; i < 4; ++i) out4[i] = v[i];
+  return LIO_OK;
+}
+
 int64_t lio_launch_count(lio_ctx* c) { return c ? c->launches : 0; }
 
 }  // extern "C"

@@ -26,6 +26,9 @@ constexpr int kTileMaxWork = 128;   // buckets per staging pass
 constexpr int kTileMaxE = 3;
 constexpr int kTileMaxSub = 2;      // sub-tiles served per tile; the remaining queries are deferred to the per-query kernel
 constexpr int kStageUnroll = 4;     // bucket loads in flight per lane while staging
+// run-time tuning knobs (defaults = the constants above; LIO_TILE_MAXSUB / LIO_TILE_MAXE at context creation)
+__device__ __constant__ int c_tile_max_sub = kTileMaxSub;
+__device__ __constant__ int c_tile_max_e = kTileMaxE;
 
 struct __align__(16) TileSmem {
   float4 pts[kTileCap];
@@ -161,13 +164,13 @@ __device__ __forceinline__ int tile_stage(const MapView& m, TileSmem& sm, int la
 // one-query sub-tiles in one warp is a chain of dependent memory latencies: the per-query kernel spreads them out).
 template <typename Emit>
 __device__ __forceinline__ unsigned tile_search(const MapView& m, TileSmem& sm, int lane, float qx, float qy, float qz, bool valid,
-                                                float max_d2, Emit&& emit) {
+                                                float max_d2, Emit&& emit, unsigned* overflow_mask = nullptr) {
   const float h = m.cell_size;
   const int cx = vox_of(qx, m.ds) >> m.cell_shift, cy = vox_of(qy, m.ds) >> m.cell_shift, cz = vox_of(qz, m.ds) >> m.cell_shift;
   const int big = 0x3fffffff;
   unsigned pending = __ballot_sync(0xFFFFFFFFu, valid);
   unsigned failed = 0;
-  for (int round = 0; round < kTileMaxSub && pending; ++round) {
+  for (int round = 0; round < c_tile_max_sub && pending; ++round) {
     // members of this sub-tile
     const int a = __ffs(pending) - 1;
     const int ax0 = __shfl_sync(0xFFFFFFFFu, cx, a), ay0 = __shfl_sync(0xFFFFFFFFu, cy, a), az0 = __shfl_sync(0xFFFFFFFFu, cz, a);
@@ -182,7 +185,7 @@ __device__ __forceinline__ unsigned tile_search(const MapView& m, TileSmem& sm, 
       const int loz = __reduce_min_sync(0xFFFFFFFFu, mine ? cz : big) - E, hiz = __reduce_max_sync(0xFFFFFFFFu, mine ? cz : -big) + E;
       const int dx = hix - lox + 1, dy = hiy - loy + 1, dz = hiz - loz + 1;
       int n_st = -1;
-      if (E <= kTileMaxE && dx * dy * dz <= kTileMaxCells) n_st = tile_stage(m, sm, lane, lox, loy, loz, dx, dy, dz);
+      if (E <= c_tile_max_e && dx * dy * dz <= kTileMaxCells) n_st = tile_stage(m, sm, lane, lox, loy, loz, dx, dy, dz);
       if (n_st < 0) {  // too many cells / candidates: these queries take the per-query path
         failed |= sub;
         break;
@@ -221,10 +224,11 @@ __device__ __forceinline__ unsigned tile_search(const MapView& m, TileSmem& sm, 
       }
       sub &= ~__ballot_sync(0xFFFFFFFFu, done);
       const int want = __reduce_max_sync(0xFFFFFFFFu, need);
-      E = max(E + 1, min(want, kTileMaxE));
+      E = max(E + 1, min(want, c_tile_max_e));
       __syncwarp();  // staged points are overwritten by the next pass
     }
   }
+  if (overflow_mask) *overflow_mask = failed;  // lanes deferred because the staging area / growth limit was exceeded
   return failed | pending;
 }
 

@@ -222,6 +222,192 @@ __global__ void k_ds_commit(MapView m, const float4* __restrict__ pts, uint32_t 
   }
 }
 
+// ---- 8-lane group forms: lane j of a group looks at slot j of a bucket, so a bucket is ONE coalesced 128-byte access
+// and the per-point chains of dependent slot reads of the thread-per-point kernels above become a ballot -----------
+struct Grp {
+  int lane, gl;
+  unsigned mask;
+  __device__ Grp() {
+    lane = threadIdx.x & 31;
+    gl = lane & 7;
+    mask = 0xFFu << (lane & 24);
+  }
+  __device__ __forceinline__ unsigned ballot(bool p) const { return (__ballot_sync(mask, p) >> (lane & 24)) & 0xFFu; }
+  template <typename T>
+  __device__ __forceinline__ T bcast(T v, int src) const { return __shfl_sync(mask, v, src, 8); }
+};
+// group index spread over the blocks like spread_index(): consecutive batch points go to different blocks
+__device__ __forceinline__ uint32_t spread_group() { return (threadIdx.x >> 3) * gridDim.x + blockIdx.x; }
+__device__ __forceinline__ uint32_t groups_total() { return gridDim.x * (blockDim.x >> 3); }
+
+// claim a free slot in the chain of entry `ei` for point (x,y,z,id); every lane of the group returns the outcome
+__device__ bool claim_slot_g(const MapView& m, const Grp& g, uint32_t ei, float x, float y, float z, uint32_t id) {
+  HashEntry* e = m.table + ei;
+  const uint32_t head = e->head;
+  uint32_t b = head, spare = kNone;
+  while (true) {
+    float4* s = m.slots + (size_t)b * kSlots;
+    uint32_t* w = reinterpret_cast<uint32_t*>(&s[g.gl].w);
+    unsigned empties = g.ballot(*reinterpret_cast<volatile uint32_t*>(w) == kEmptyId);
+    while (empties) {
+      const int j = __ffs(empties) - 1;
+      int won = 0;
+      if (g.gl == j) won = atomicCAS(w, kEmptyId, id) == kEmptyId;
+      won = g.bcast(won, j);
+      if (won) {
+        if (g.gl == j) {
+          s[j].x = x;
+          s[j].y = y;
+          s[j].z = z;
+        }
+        return true;
+      }
+      empties &= empties - 1;
+    }
+    // bucket full: follow the chain, linking a new bucket at its tail when needed (lane 0 does the bookkeeping)
+    uint32_t nb = kNone;
+    int fail = 0;
+    if (g.gl == 0) {
+      uint32_t* link = (b == head) ? &e->ovf : &m.next[b];
+      nb = *reinterpret_cast<volatile uint32_t*>(link);
+      if (nb == kNone) {
+        if (spare == kNone) {
+          spare = atomicAdd(&m.ctr->pool_top, 1u);
+          if (spare >= m.pool_cap) {
+            atomicOr(&m.ctr->error, kErrPoolFull);
+            fail = 1;
+          }
+        }
+        if (!fail) {
+          const uint32_t prev = atomicCAS(link, kNone, spare);
+          if (prev == kNone) {
+            nb = spare;
+            spare = kNone;
+          } else {
+            nb = prev;
+          }
+        }
+      }
+    }
+    fail = g.bcast(fail, 0);
+    if (fail) return false;
+    b = g.bcast(nb, 0);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_insert_plain_g(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
+                                                        const uint32_t* __restrict__ ent) {
+  const Grp g;
+  const uint32_t n = batch_n(n_max, n_dev);
+  const uint32_t base = m.ctr->next_id;
+  for (uint32_t i = spread_group(); i < n; i += groups_total()) {
+    const uint32_t ei = ent[i];
+    if (ei == kNone) continue;
+    const float4 p = pts[i];
+    if (claim_slot_g(m, g, ei, p.x, p.y, p.z, base + i) && g.gl == 0) atomicAdd(&m.ctr->live, 1);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_ds_scan_g(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
+                                                   const uint32_t* __restrict__ ent, unsigned long long* vox_keys,
+                                                   unsigned long long* vox_best, uint32_t vox_mask, uint32_t* __restrict__ tslot,
+                                                   unsigned long long* __restrict__ ebest, uint32_t* __restrict__ ecnt) {
+  const Grp g;
+  const uint32_t n = batch_n(n_max, n_dev);
+  for (uint32_t i = spread_group(); i < n; i += groups_total()) {
+    const uint32_t ei = ent[i];
+    if (ei == kNone) {
+      if (g.gl == 0) tslot[i] = kNone;
+      continue;
+    }
+    const float4 p = pts[i];
+    const int kx = vox_of(p.x, m.ds), ky = vox_of(p.y, m.ds), kz = vox_of(p.z, m.ds);
+    float mx, my, mz;
+    voxel_centre(kx, ky, kz, m.ds, mx, my, mz);
+    unsigned long long best = ~0ull;
+    uint32_t cnt = 0;
+    const HashEntry e = m.table[ei];
+    for (uint32_t b = e.head; b != kNone; b = chain_next(m, e.head, e.ovf, b)) {
+      const float4 q = m.slots[(size_t)b * kSlots + g.gl];
+      const uint32_t id = __float_as_uint(q.w);
+      const bool hit = id != kEmptyId && vox_of(q.x, m.ds) == kx && vox_of(q.y, m.ds) == ky && vox_of(q.z, m.ds) == kz;
+      cnt += __popc(g.ballot(hit));
+      if (hit) {
+        const unsigned long long k = key64(sqdist3(q.x, q.y, q.z, mx, my, mz), id);
+        if (k < best) best = k;
+      }
+    }
+#pragma unroll
+    for (int off = 4; off; off >>= 1) {
+      const unsigned long long o = __shfl_xor_sync(g.mask, best, off, 8);
+      if (o < best) best = o;
+    }
+    if (g.gl == 0) {
+      ebest[i] = best;
+      ecnt[i] = cnt;
+      const unsigned long long vkey = pack3(kx, ky, kz);
+      uint32_t s = hash64(vkey) & vox_mask;
+      while (true) {
+        unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&vox_keys[s]);
+        if (cur == kEmptyKey) cur = atomicCAS(&vox_keys[s], kEmptyKey, vkey);
+        if (cur == kEmptyKey || cur == vkey) break;
+        s = (s + 1) & vox_mask;
+      }
+      const float d = sqdist3(p.x, p.y, p.z, mx, my, mz);
+      atomicMin(&vox_best[s], ((unsigned long long)__float_as_uint(d) << 32) | (0xFFFFFFFFu - i));
+      tslot[i] = s;
+    }
+  }
+}
+
+// group form of erase_voxel
+__device__ void erase_voxel_g(const MapView& m, const Grp& g, const HashEntry& e, int kx, int ky, int kz, uint32_t base_id, uint32_t keep) {
+  for (uint32_t b = e.head; b != kNone; b = chain_next(m, e.head, e.ovf, b)) {
+    float4* s = m.slots + (size_t)b * kSlots + g.gl;
+    uint32_t* w = reinterpret_cast<uint32_t*>(&s->w);
+    const uint32_t id = *reinterpret_cast<volatile uint32_t*>(w);
+    if (id == kEmptyId || id >= base_id || id == keep) continue;
+    const float x = *reinterpret_cast<volatile float*>(&s->x), y = *reinterpret_cast<volatile float*>(&s->y),
+                z = *reinterpret_cast<volatile float*>(&s->z);
+    if (vox_of(x, m.ds) != kx || vox_of(y, m.ds) != ky || vox_of(z, m.ds) != kz) continue;
+    atomicCAS(w, id, kEmptyId);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_ds_commit_g(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
+                                                     const uint32_t* __restrict__ ent, const unsigned long long* __restrict__ vox_best,
+                                                     const uint32_t* __restrict__ tslot, const unsigned long long* __restrict__ ebest,
+                                                     const uint32_t* __restrict__ ecnt) {
+  const Grp g;
+  const uint32_t n = batch_n(n_max, n_dev);
+  const uint32_t base = m.ctr->next_id;
+  for (uint32_t i = spread_group(); i < n; i += groups_total()) {
+    const uint32_t ts = tslot[i];
+    if (ts == kNone) continue;
+    const float4 p = pts[i];
+    const int kx = vox_of(p.x, m.ds), ky = vox_of(p.y, m.ds), kz = vox_of(p.z, m.ds);
+    float mx, my, mz;
+    voxel_centre(kx, ky, kz, m.ds, mx, my, mz);
+    const uint32_t dbits = __float_as_uint(sqdist3(p.x, p.y, p.z, mx, my, mz));
+    if (vox_best[ts] != (((unsigned long long)dbits << 32) | (0xFFFFFFFFu - i))) continue;  // not the voxel's winner
+    const uint32_t ei = ent[i];
+    const HashEntry e = m.table[ei];
+    const unsigned long long eb = ebest[i];
+    const uint32_t ec = ecnt[i];
+    if (ec == 0 || dbits <= (uint32_t)(eb >> 32)) {
+      if (ec) erase_voxel_g(m, g, e, kx, ky, kz, base, kEmptyId);
+      __syncwarp(g.mask);
+      if (claim_slot_g(m, g, ei, p.x, p.y, p.z, base + i) && g.gl == 0) {
+        atomicAdd(&m.ctr->live, 1 - (int)ec);
+        atomicAdd(&m.ctr->batch_alive, 1u);
+      }
+    } else if (ec > 1) {
+      erase_voxel_g(m, g, e, kx, ky, kz, base, (uint32_t)eb);
+      if (g.gl == 0) atomicAdd(&m.ctr->live, -(int)(ec - 1));
+    }
+  }
+}
+
 __global__ void k_advance_ids(MapCounters* ctr, uint32_t n_max, const uint32_t* n_dev) {
   ctr->next_id += batch_n(n_max, n_dev);
 }
@@ -361,11 +547,12 @@ int map_add_device(lio_ctx* c, const float4* pts, uint32_t n_max, const uint32_t
   int rc = map_ensure_batch(c, n_max);
   if (rc) return rc;
   const int block = 256, grid = grid_for(c, n_max, block);
+  const int ggrid = grid_for(c, (uint32_t)std::min<uint64_t>((uint64_t)n_max * 8, 0x7FFFFFFFull), block);  // 8 lanes per point
   MapView& m = c->map;
   timer_begin(c, T_INSERT);
   k_cells_ensure<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent);
   if (!downsample) {
-    k_insert_plain<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent);
+    k_insert_plain_g<<<ggrid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent);
     c->launches += 2;
   } else {
     // the arbitration table only needs to cover this batch
@@ -373,10 +560,10 @@ int map_add_device(lio_ctx* c, const float4* pts, uint32_t n_max, const uint32_t
     cudaMemsetAsync(c->vox_keys, 0xFF, sizeof(unsigned long long) * (size_t)vcap, c->stream);
     cudaMemsetAsync(c->vox_best, 0xFF, sizeof(unsigned long long) * (size_t)vcap, c->stream);
     k_reset_batch<<<1, 1, 0, c->stream>>>(m.ctr);
-    k_ds_scan<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent, c->vox_keys, c->vox_best, vcap - 1,
-                                             c->batch_tslot, c->batch_ebest, c->batch_ecnt);
-    k_ds_commit<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent, c->vox_best, c->batch_tslot,
-                                               c->batch_ebest, c->batch_ecnt);
+    k_ds_scan_g<<<ggrid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent, c->vox_keys, c->vox_best, vcap - 1,
+                                                c->batch_tslot, c->batch_ebest, c->batch_ecnt);
+    k_ds_commit_g<<<ggrid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent, c->vox_best, c->batch_tslot,
+                                                  c->batch_ebest, c->batch_ecnt);
     c->launches += 4;
   }
   k_advance_ids<<<1, 1, 0, c->stream>>>(m.ctr, n_max, n_dev);

@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
                                                                int n, StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
                                                                float* __restrict__ nn_d2, int* __restrict__ nn_cnt,
                                                                uint32_t* __restrict__ ctr, uint32_t* __restrict__ left,
-                                                               const IekfCtl* __restrict__ ctl) {
+                                                               const IekfCtl* __restrict__ ctl, uint32_t* __restrict__ stats) {
   __shared__ TileSmem smem[kTileWarps];
   __shared__ StateArg s_st;
   if (DEV && (ctl->finished || !ctl->converge)) return;  // cached neighbours are reused (ekfom_data.converge == false)
@@ -142,6 +142,7 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
       qx = b.x, qy = b.y, qz = b.z;
       if (XFORM) body_to_world(st, b.x, b.y, b.z, qx, qy, qz);
     }
+    unsigned overflow = 0;
     const unsigned pending = tile_search(m, sm, lane, qx, qy, qz, valid, max_d2, [&](const Top32& L, int cnt) {
       cnt = min(cnt, k);
       const uint32_t ks[kK] = {L.b0, L.b1, L.b2, L.b3, L.b4};
@@ -154,8 +155,12 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
           if (nn_d2) nn_d2[(size_t)i * k + j] = have ? __uint_as_float(ks[j]) : inf;
         }
       nn_cnt[i] = cnt;
-    });
+    }, &overflow);
     if (pending) {  // defer to k_knn_left
+      if (lane == 0 && stats) {  // [1] staging overflow / growth limit, [2] tile too incoherent (beyond kTileMaxSub sub-tiles)
+        if (overflow) atomicAdd(stats + 1, (uint32_t)__popc(overflow));
+        if (pending & ~overflow) atomicAdd(stats + 2, (uint32_t)__popc(pending & ~overflow));
+      }
       uint32_t base = 0;
       if (lane == 0) base = atomicAdd(ctr + 1, (uint32_t)__popc(pending));
       base = __shfl_sync(0xFFFFFFFFu, base, 0);
@@ -399,19 +404,22 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
   __shared__ double s_part[kRedWarps][NV];
   __shared__ __align__(16) double s_out[160];
   for (int e = threadIdx.x; e < 160; e += blockDim.x) s_out[e] = 0.0;
-  if (lane < NV) {
+  // (the loads of a batch are issued together; the additions keep their fixed order, absent blocks add +0.0)
+  for (int v = lane; v < NV; v += 32) {
     const int nb = gridDim.x;
     double sum = 0.0;
-    for (int b = warp; b < nb; b += kRedWarps) sum += __ldcg(partials + (size_t)b * kMaxVals + lane);
-    s_part[warp][lane] = sum;
-  }
-  if (NV > 32) {  // 12-column form: values 32..NV-1
-    for (int v = 32 + lane; v < NV; v += 32) {
-      const int nb = gridDim.x;
-      double sum = 0.0;
-      for (int b = warp; b < nb; b += kRedWarps) sum += __ldcg(partials + (size_t)b * kMaxVals + v);
-      s_part[warp][v] = sum;
+    constexpr int U = 8;
+    for (int b0 = warp; b0 < nb; b0 += kRedWarps * U) {
+      double t[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int b = b0 + u * kRedWarps;
+        t[u] = (b < nb) ? __ldcg(partials + (size_t)b * kMaxVals + v) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) sum += t[u];
     }
+    s_part[warp][v] = sum;
   }
   __syncthreads();
   if (threadIdx.x < NV) {
@@ -670,6 +678,15 @@ int scan_alloc(lio_ctx* c) {
   {
     const char* e = getenv("LIO_KNN_MODE");
     c->knn_mode = (e && std::strcmp(e, "group") == 0) ? 0 : 1;
+    {  // tuning knobs of the tile search (process-wide constants: written on every context creation)
+      e = getenv("LIO_TILE_MAXSUB");
+      const int sub = e ? std::max(1, std::min(32, atoi(e))) : kTileMaxSub;
+      e = getenv("LIO_TILE_MAXE");
+      const int me = e ? std::max(1, std::min(8, atoi(e))) : kTileMaxE;
+      LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_max_sub, &sub, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
+      LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_max_e, &me, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
+      LIO_CUDA(cudaStreamSynchronize(c->stream));
+    }
     e = getenv("LIO_IEKF_MODE");
     c->iekf_mode = (e && std::strcmp(e, "device") == 0) ? 1 : 0;
   }
@@ -794,12 +811,12 @@ int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
     c->tile_flip ^= 1;
     if (dev_loop) {
       k_knn_tile<true, true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
-                                                                                  c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], c->iekf_ctl);
+                                                                                  c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], c->iekf_ctl, c->tile_stats);
       k_knn_left<true, true><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
                                                                          c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, c->iekf_ctl);
     } else {
       k_knn_tile<true, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
-                                                                                   c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], nullptr);
+                                                                                   c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats);
       k_knn_left<true, false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
                                                                           c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, nullptr);
     }
@@ -827,7 +844,7 @@ int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float
     uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
     c->tile_flip ^= 1;
     k_knn_tile<false, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, q_dev, c->tile_vals[1], n, st, k, max_d2, out_nn,
-                                                                                  out_d2, out_cnt, ctr, c->tile_vals[0], nullptr);
+                                                                                  out_d2, out_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats);
     k_knn_left<false, false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
                                                                          ctr, ctr_next, c->tile_stats, nullptr);
     c->launches += 1;

@@ -273,3 +273,36 @@ def make_keyframes(scene, n_pass=40, step=1.0, kind="vlp16", n_az=None, max_rang
             est.append(T.copy())
         stamps.append(float(i))
     return clouds, est, true, stamps
+
+
+# ------------------------------------------------------------------------------------------- IMU
+def imu_noise_cov(gyr_cov=0.1, acc_cov=0.1, b_gyr_cov=1e-4, b_acc_cov=1e-4):
+    """Process noise Q (12x12) over (gyro, acc, gyro-bias, acc-bias) with the values of kitti.yaml:16-19."""
+    return np.diag([gyr_cov] * 3 + [acc_cov] * 3 + [b_gyr_cov] * 3 + [b_acc_cov] * 3).astype(np.float64)
+
+
+def make_imu_segment(state0, n_imu=20, scan_period=0.1, omega=(0.05, -0.03, 0.4), acc_body=(0.6, -0.2, 0.1), seed=SEED + 300):
+    """IMU samples over one scan period for a platform that turns at `omega` (rad/s, body) and accelerates at `acc_body`
+    (m/s^2, body, gravity removed): returns (dt, gyro[n,3], acc[n,3]) with acc the specific force the sensor reads at the
+    start pose (R^T (a_w - g) is what get_f inverts), plus small white noise."""
+    rng = np.random.default_rng(seed)
+    R = np.asarray(state0[3:12]).reshape(3, 3)
+    g = np.asarray(state0[33:36])
+    dt = scan_period / n_imu
+    gyro = np.tile(np.asarray(omega, np.float64), (n_imu, 1)) + rng.normal(0, 1e-3, (n_imu, 3))
+    acc = np.tile(np.asarray(acc_body, np.float64) - R.T @ g, (n_imu, 1)) + rng.normal(0, 1e-2, (n_imu, 3))
+    return dt, gyro, acc
+
+
+def propagate_poses(predict, state0, P0, dt, gyro, acc, Q):
+    """ImuProcess::UndistortPcl's forward pass with `predict` = esekfom::predict (product or oracle): returns the Pose6D
+    rows (n+1, 22: offset_time | acc_s | angvel | vel | pos | rot) and the propagated (state, P) at the scan end."""
+    s, P = np.array(state0, np.float64), np.array(P0, np.float64)
+    rows = [np.concatenate([[0.0], np.zeros(3), np.zeros(3), s[24:27], s[0:3], s[3:12]])]
+    for k in range(len(gyro)):
+        s, P = predict(s, P, dt, acc[k], gyro[k], Q)
+        R = s[3:12].reshape(3, 3)
+        angvel = gyro[k] - s[27:30]
+        acc_s = R @ (acc[k] - s[30:33]) + s[33:36]
+        rows.append(np.concatenate([[dt * (k + 1)], acc_s, angvel, s[24:27], s[0:3], s[3:12]]))
+    return np.array(rows), s, P

@@ -138,6 +138,9 @@ int lio_timing_get(lio_ctx* ctx, const char* name, double* mean_ms, int* launche
 int lio_timing_reset(lio_ctx* ctx);
 /* queries of all searches so far that left the shared-memory tile path for the per-query fallback search */
 int lio_knn_stats(lio_ctx* ctx, uint64_t* fallback_queries);
+/* out4: [0] queries finished by the per-query kernel, [1] of those deferred because a tile's staging area or growth limit
+ * overflowed, [2] deferred because the tile was too incoherent, [3] reserved.  Running totals since context creation. */
+int lio_knn_stats_detail(lio_ctx* ctx, uint64_t* out4);
 /* Achievable random-gather bandwidth of the device: random 16-byte loads from a table of `table_bytes` (use >= 320 MB so
  * it exceeds L2).  *gbps_16B counts the 16 requested bytes per load, *gbps_sector the 32-byte sectors they drag. */
 int lio_gather_probe(lio_ctx* ctx, uint64_t table_bytes, int reps, double* gbps_16B, double* gbps_sector);
