@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="iekf", choices=["iekf", "loop", "knn_sweep", "map_growth"])
+    ap.add_argument("--workload", default="iekf", choices=["iekf", "loop", "knn_sweep", "map_growth", "sequence"])
     ap.add_argument("--scans", type=int, default=4, help="distinct synthetic scans cycled through")
     ap.add_argument("--n-scan", type=int, default=N_SCAN)
     ap.add_argument("--n-map", type=int, default=N_MAP)
@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--n-pass", type=int, default=100, help="loop workload: keyframes per pass of the out-and-back drive")
     ap.add_argument("--sweep-map", type=int, default=20_000_000, help="knn_sweep workload: map points")
     ap.add_argument("--sweep-queries", type=int, default=100_000, help="knn_sweep workload: queries per call")
+    ap.add_argument("--seq-scans", type=int, default=100, help="sequence workload: VLP-16 scans (configs[0] names 1000)")
     ap.add_argument("--map-scans", type=int, default=200, help="map_growth workload: Avia-shaped scans along the drive")
     ap.add_argument("--map-check-every", type=int, default=50, help="map_growth workload: compare the live set with the oracle every N scans")
     ap.add_argument("--no-loop", action="store_true", help="iekf workload: skip the loop_icp section of the JSON line")
@@ -335,6 +336,8 @@ def main():
     if args.workload == "loop":
         loop_bench = importlib.import_module("bench_loop")
         return loop_bench.main(args)
+    if args.workload == "sequence":
+        return importlib.import_module("bench_seq").main(args)
     if args.workload == "map_growth":
         return importlib.import_module("bench_map").main(args)
     if args.workload == "knn_sweep":

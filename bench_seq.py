@@ -1,0 +1,196 @@
+"""BASELINE.json configs[0]: synthetic VLP-16-shaped sequence (28,800 rays/scan, 0.5 m voxel filter, synthetic IMU at 200 Hz)
+through the whole per-scan chain, on the CPU oracle and on the GPU path, with the trajectory error between the two.
+
+  python bench.py --workload sequence [--seq-scans 100]
+
+Per scan, as the reference's main loop does it (laserMapping.cpp / IMU_Processing.hpp, absent submodule; SURVEY.md §3,
+§8(f)): IMU forward propagation (esekfom predict per IMU sample) -> UndistortPcl back-compensation of the raw scan ->
+VoxelGrid at filter_size_surf -> lasermap_fov_segment -> update_iterated_dyn_share_modified (h_share_model inside) ->
+map_incremental.  The GPU side runs lio_imu_predict (host FP64), lio_scan_undistort, loop_voxelize, lio_fov_segment and
+lio_iekf_update_map; the oracle side runs the restatements of the same steps.  Both consume identical raw scans and IMU
+samples and run free (each feeds its own estimate forward).  Reported: scans/s of each side, ATE of each against the
+generating trajectory, and the GPU-vs-oracle trajectory divergence (north_star bar: < 1 mm).
+
+The scene is the seeded street scene of synth.py.  The motion is generated from the IMU side: body rates and world
+accelerations are drawn piecewise-constant per IMU sample and integrated with the very discrete model the filter
+propagates with, so the truth is exactly reachable; every scan is ray-cast in 20 time slices, each from the pose the
+platform has at that slice's time, which is what makes the raw scans motion-distorted.
+"""
+import importlib
+import json
+import time
+
+import numpy as np
+
+IMU_PER_SCAN = 20
+SCAN_PERIOD = 0.1
+FILTER_SURF = 0.5
+
+
+def make_motion(synth, n_scans, seed=4242):
+    """Truth at IMU rate: returns dict(R[k], p[k], v[k], gyro[k], acc[k] (specific force), a_w[k]) for k = 0..n_scans*20."""
+    rng = np.random.default_rng(seed)
+    dt = SCAN_PERIOD / IMU_PER_SCAN
+    n = n_scans * IMU_PER_SCAN
+    g = synth.default_grav()
+    R = synth.rot_from_rpy(0.0, 0.0, 0.1)
+    p = np.array([-0.45 * n_scans * 0.5, 1.0, 1.8])
+    v = R @ np.array([5.0, 0.0, 0.0])
+    Rs, ps, vs, gy, ac = [R], [p], [v], [], []
+    for k in range(n):
+        tt = k * dt
+        omega = np.array([0.02 * np.sin(1.3 * tt), 0.015 * np.cos(0.9 * tt), 0.25 * np.sin(0.5 * tt)])  # body rates
+        a_w = np.array([0.8 * np.sin(0.7 * tt), 0.6 * np.cos(0.4 * tt), 0.05 * np.sin(2.0 * tt)])  # world acceleration
+        gy.append(omega)
+        ac.append(R.T @ (a_w - g))
+        p = p + v * dt
+        R = R @ synth.so3_exp(omega * dt)
+        v = v + a_w * dt
+        Rs.append(R), ps.append(p), vs.append(v)
+    noise_g = rng.normal(0, 2e-4, (n, 3))
+    noise_a = rng.normal(0, 2e-3, (n, 3))
+    return dict(R=Rs, p=ps, v=vs, gyro=np.array(gy), acc=np.array(ac), gyro_meas=np.array(gy) + noise_g,
+                acc_meas=np.array(ac) + noise_a, dt=dt, grav=g)
+
+
+def make_raw_scan(synth, scene, motion, i, seed):
+    """VLP-16 scan i, ray-cast in IMU_PER_SCAN azimuth slices, each from the truth pose at the slice's IMU tick plus the
+    intra-segment model at the slice's mid time.  Returns body points (n, 3) f32 in ring-major order and t_ms (n,) f32."""
+    rng = np.random.default_rng(seed)
+    dirs = synth.lidar_dirs("vlp16").reshape(16, 1800, 3)
+    cols = 1800 // IMU_PER_SCAN
+    dt = motion["dt"]
+    pts, tms = [], []
+    for s in range(IMU_PER_SCAN):
+        k = i * IMU_PER_SCAN + s
+        d_mid = 0.5 * dt
+        R = motion["R"][k] @ synth.so3_exp(motion["gyro"][k] * d_mid)
+        a_w = motion["R"][k] @ motion["acc"][k] + motion["grav"]
+        p = motion["p"][k] + motion["v"][k] * d_mid + 0.5 * a_w * d_mid * d_mid
+        db = dirs[:, s * cols:(s + 1) * cols].reshape(-1, 3)
+        dist = synth.raycast(scene, p, db @ R.T, 100.0)
+        ok = np.isfinite(dist)
+        dist = dist[ok] + rng.normal(0, 0.02, ok.sum())
+        pts.append((db[ok] * dist[:, None]).astype(np.float32))
+        tms.append(np.full(ok.sum(), 1e3 * (s * dt + d_mid), np.float32))
+    pts, tms = np.concatenate(pts), np.concatenate(tms)
+    order = np.argsort(tms, kind="stable")  # UndistortPcl sorts the cloud by curvature first
+    return np.ascontiguousarray(pts[order]), np.ascontiguousarray(tms[order])
+
+
+class GpuSide:
+    name = "gpu"
+
+    def __init__(self, pkg, loop_mod, kw):
+        self.pkg = pkg
+        self.ctx = pkg.LioContext(0.5, max_points=1 << 22, max_scan=1 << 16, **kw)
+        self.lc = loop_mod.LoopClosure()
+        self.predict = pkg.imu_predict
+
+    def undistort(self, pts, t_ms, rows, s_end):
+        self.ctx.scan_upload(pts)
+        self.ctx.scan_undistort(t_ms, rows, s_end)
+        return self.ctx.scan_body()
+
+    def voxelize(self, pts):
+        xyzi = np.concatenate([pts, np.zeros((len(pts), 1), np.float32)], 1)
+        return np.ascontiguousarray(self.lc.voxelize_pcd(xyzi, FILTER_SURF)[:, :3])
+
+    def update(self, down, s, P):
+        self.ctx.scan_upload(down)
+        s, P, _ = self.ctx.iekf_update_map(s, P, True)
+        return s, P
+
+    def close(self):
+        self.ctx.close()
+
+
+class OracleSide:
+    name = "oracle"
+
+    def __init__(self, orc, kw):
+        self.orc = orc
+        self.ctx = orc.OracleLio(0.5, nthreads=orc.max_threads(), **kw)
+        self.predict = orc.imu_predict
+
+    def undistort(self, pts, t_ms, rows, s_end):
+        return self.orc.undistort(pts, t_ms, rows, s_end)
+
+    def voxelize(self, pts):
+        xyzi = np.concatenate([pts, np.zeros((len(pts), 1), np.float32)], 1)
+        return np.ascontiguousarray(self.orc.voxelize(xyzi, FILTER_SURF)[:, :3])
+
+    def update(self, down, s, P):
+        self.ctx.scan_upload(down)
+        s, P, _ = self.ctx.iekf_update(s, P)
+        self.ctx.map_incremental(s, True)
+        return s, P
+
+    def close(self):
+        self.ctx.close()
+
+
+def run_side(side, synth, motion, scans, s0, P0, Q):
+    """Free-running filter over the sequence; returns (positions (n,3), seconds, mean points per filtered scan)."""
+    s, P = np.array(s0), np.array(P0)
+    traj, busy, n_down = [], 0.0, 0
+    for i, (pts, t_ms) in enumerate(scans):
+        a, b = i * IMU_PER_SCAN, (i + 1) * IMU_PER_SCAN
+        t0 = time.perf_counter()
+        rows, s_end, P_end = synth.propagate_poses(side.predict, s, P, motion["dt"], motion["gyro_meas"][a:b], motion["acc_meas"][a:b], Q)
+        und = side.undistort(pts, t_ms, rows, s_end)
+        down = side.voxelize(und)
+        if i == 0:  # first scan initialises the map at the propagated pose (no update yet), as the reference does
+            R, p = s_end[3:12].reshape(3, 3), s_end[0:3]
+            side.ctx.map_build((down.astype(np.float64) @ R.T + p).astype(np.float32))
+            s, P = s_end, P_end
+        else:
+            side.ctx.fov_segment(s_end[0:3])
+            s, P = side.update(down, s_end, P_end)
+        busy += time.perf_counter() - t0
+        n_down += len(down)
+        traj.append(s[0:3].copy())
+    return np.array(traj), busy, n_down / len(scans)
+
+
+def main(args):
+    pkg = importlib.import_module("fast-lio-sam_gps_b200")
+    synth = importlib.import_module("fast-lio-sam_gps_b200.synth")
+    loop_mod = importlib.import_module("fast-lio-sam_gps_b200.loop")
+    from oracle import orc
+
+    orc.build()
+    n = args.seq_scans
+    motion = make_motion(synth, n)
+    scene = synth.make_scene(half_extent=max(80.0, 0.3 * n + 60.0))
+    t0 = time.perf_counter()
+    scans = [make_raw_scan(synth, scene, motion, i, 9000 + i) for i in range(n)]
+    gen_s = time.perf_counter() - t0
+    s0 = synth.make_state(motion["R"][0], motion["p"][0])
+    s0[24:27] = motion["v"][0]
+    P0, Q = synth.default_cov(), synth.imu_noise_cov(gyr_cov=1e-4, acc_cov=1e-2, b_gyr_cov=1e-6, b_acc_cov=1e-6)
+    kw = dict(cube_side_length=200.0, det_range=50.0)
+    g = GpuSide(pkg, loop_mod, kw)
+    o = OracleSide(orc, kw)
+    g_traj, g_s, g_pts = run_side(g, synth, motion, scans, s0, P0, Q)
+    o_traj, o_s, _ = run_side(o, synth, motion, scans, s0, P0, Q)
+    truth = np.array([motion["p"][(i + 1) * IMU_PER_SCAN] for i in range(n)])
+    rmse = lambda a, b: float(np.sqrt(np.mean(np.sum((a - b) ** 2, 1))))
+    div = rmse(g_traj, o_traj)
+    line = {
+        "metric": "VLP-16 sequence scans/s (IMU propagate + undistort + voxel filter + IEKF + map update)", "value": n / g_s,
+        "unit": "scans/s", "n_gpus": 1, "higher_is_better": True, "data": "synthetic", "dtype": "f32 points, f64 state",
+        "config": {"workload": "configs[0]: synthetic VLP-16-shaped sequence, 0.5 m voxel filter, synthetic IMU at 200 Hz",
+                   "scans": n, "raw_points_per_scan": int(np.mean([len(p) for p, _ in scans])), "filtered_points_per_scan": round(g_pts),
+                   "imu_per_scan": IMU_PER_SCAN, "timing": "wall clock, host buffers, every stage through the C-ABI"},
+        "ate_gpu_vs_truth_m": rmse(g_traj, truth), "ate_oracle_vs_truth_m": rmse(o_traj, truth),
+        "ate_gpu_vs_oracle_m": div, "max_divergence_m": float(np.abs(g_traj - o_traj).max()), "bar_m": 1e-3,
+        "cpu_baseline": {"value": n / o_s, "unit": "scans/s", "cores": orc.max_threads(), "kind": "port",
+                         "sample": f"the same {n} scans through the oracle restatement of every stage"},
+        "generation_s": gen_s,
+    }
+    print(json.dumps(line))
+    g.close()
+    o.close()
+    if not div < 1e-3:
+        raise SystemExit(f"sequence: GPU trajectory diverges from the oracle's by {div} m (bar 1 mm)")

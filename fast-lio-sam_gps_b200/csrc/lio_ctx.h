@@ -4,6 +4,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <string>
+#include <utility>
 #include <vector>
 #include <cuda_runtime.h>
 #include "../../include/lio_b200.h"
@@ -85,6 +86,15 @@ struct lio_ctx {
   size_t tile_tmp_bytes = 0;
   uint32_t tile_cap = 0;
   bool order_valid = false;      // tile_vals[1] holds the order of the current scan
+  std::vector<std::pair<int, void*>> sort_graphs;  // (padded size, cudaGraphExec_t) of the captured keys + sort passes
+  bool sort_graph_ok = true;     // false after a failed capture (LIO_SORT_GRAPH=0 disables it up front)
+  void* keys_args_host = nullptr;  // pinned KeysArgs staged by the graph's memcpy node
+  void* keys_args_dev = nullptr;
+  std::vector<std::pair<int, void*>> map_graphs;  // (2 * padded size + flg_ekf_inited, cudaGraphExec_t) of map_incremental
+  bool map_graph_ok = true;      // LIO_MAP_GRAPH=0 disables the captured form
+  int map_graph_launches = 0;    // kernels inside one map_incremental graph
+  void* map_args_host = nullptr;
+  void* map_args_dev = nullptr;
   uint32_t* tile_stats = nullptr;  // [0] queries that went to the per-query fallback (debug/bench counter)
   int tile_flip = 0;             // which counter pair the next search uses
   int knn_mode = 1;              // 1 tile (default), 0 per-query groups (LIO_KNN_MODE=group)

@@ -520,6 +520,8 @@ int map_clear(lio_ctx* c) {
 
 int map_ensure_batch(lio_ctx* c, uint32_t n) {
   if (n <= c->batch_cap) return LIO_OK;
+  for (auto& g : c->map_graphs) cudaGraphExecDestroy((cudaGraphExec_t)g.second);  // they captured the old scratch buffers
+  c->map_graphs.clear();
   cudaFree(c->batch_pts);
   cudaFree(c->batch_ent);
   cudaFree(c->batch_tslot);

@@ -97,6 +97,32 @@ __global__ void __launch_bounds__(256) k_tile_keys(MapView m, const float4* __re
   }
 }
 
+// Graph form of k_tile_keys: (state, n) come from a small device block refreshed by a memcpy node, so one captured graph
+// (keys + the library's radix-sort passes) serves every scan of up to n_pad points; rows n..n_pad-1 carry the maximal key.
+struct KeysArgs {
+  double s[36];
+  int n;
+  int pad;
+};
+__global__ void __launch_bounds__(256) k_tile_keys_g(MapView m, const float4* __restrict__ pts, const KeysArgs* __restrict__ a, int n_pad,
+                                                     uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+  __shared__ StateArg s_st;
+  if (threadIdx.x < 36) s_st.s[threadIdx.x] = a->s[threadIdx.x];
+  __syncthreads();
+  const int n = a->n;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pad; i += gridDim.x * blockDim.x) {
+    uint32_t key = (1u << kTileKeyBits) - 1u;
+    if (i < n) {
+      const float4 b = __ldg(pts + i);
+      float qx, qy, qz;
+      body_to_world(s_st, b.x, b.y, b.z, qx, qy, qz);
+      key = tile_key(m, qx, qy, qz);
+    }
+    keys[i] = key;
+    vals[i] = (uint32_t)i;
+  }
+}
+
 constexpr int kTileWarps = 4;
 
 // DEV kernels belong to the device-resident IEKF loop (lio_iekf.cuh): the state comes from ctl->x instead of the launch
@@ -462,7 +488,9 @@ template <bool DEV>
 __global__ void __launch_bounds__(256) k_classify(const float4* __restrict__ body, int n, StateArg st_param, const float4* __restrict__ nn,
                                                   const int* __restrict__ nn_cnt, int flg_ekf_inited, float fs, MapCounters* ctr,
                                                   float4* __restrict__ world, uint8_t* __restrict__ cls,
-                                                  uint32_t* __restrict__ blk_cnt, const IekfCtl* __restrict__ ctl) {
+                                                  uint32_t* __restrict__ blk_cnt, const IekfCtl* __restrict__ ctl,
+                                                  const int* __restrict__ n_ptr) {
+  if (n_ptr) n = *n_ptr;  // graph form: the grid covers the padded size, the true size sits in device memory
   __shared__ uint32_t s_cnt[2];
   __shared__ StateArg s_st;
   if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
@@ -563,7 +591,8 @@ __global__ void __launch_bounds__(1024) k_scan_blocks(uint32_t* __restrict__ blk
 // ordered scatter of the world points into PointToAdd / PointNoNeedDownsample
 __global__ void __launch_bounds__(256) k_scatter_lists(const float4* __restrict__ world, const uint8_t* __restrict__ cls, int n,
                                                        const uint32_t* __restrict__ blk_off, float4* __restrict__ list_add,
-                                                       float4* __restrict__ list_nodown) {
+                                                       float4* __restrict__ list_nodown, const int* __restrict__ n_ptr) {
+  if (n_ptr) n = *n_ptr;
   __shared__ uint32_t s_w[2][8];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -687,6 +716,10 @@ int scan_alloc(lio_ctx* c) {
       LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_max_e, &me, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
       LIO_CUDA(cudaStreamSynchronize(c->stream));
     }
+    e = getenv("LIO_SORT_GRAPH");
+    c->sort_graph_ok = !(e && std::strcmp(e, "0") == 0);
+    e = getenv("LIO_MAP_GRAPH");
+    c->map_graph_ok = !(e && std::strcmp(e, "0") == 0);
     e = getenv("LIO_IEKF_MODE");
     c->iekf_mode = (e && std::strcmp(e, "device") == 0) ? 1 : 0;
   }
@@ -726,6 +759,14 @@ void scan_free(lio_ctx* c) {
     cudaFree(c->tile_vals[j]);
   }
   if (c->out_host) cudaFreeHost(c->out_host);
+  for (auto& g : c->sort_graphs) cudaGraphExecDestroy((cudaGraphExec_t)g.second);
+  c->sort_graphs.clear();
+  for (auto& g : c->map_graphs) cudaGraphExecDestroy((cudaGraphExec_t)g.second);
+  c->map_graphs.clear();
+  if (c->map_args_host) cudaFreeHost(c->map_args_host);
+  cudaFree(c->map_args_dev);
+  if (c->keys_args_host) cudaFreeHost(c->keys_args_host);
+  cudaFree(c->keys_args_dev);
   cudaFree(c->iekf_ctl);
   cudaFree(c->scan_t);
   cudaFree(c->imu_pose);
@@ -752,6 +793,8 @@ int scan_undistort(lio_ctx* c, const float* t_ms_host, const double* pose_host, 
 
 int tile_ensure(lio_ctx* c, uint32_t n) {
   if (n <= c->tile_cap) return LIO_OK;
+  for (auto& g : c->sort_graphs) cudaGraphExecDestroy((cudaGraphExec_t)g.second);  // they captured the old buffers
+  c->sort_graphs.clear();
   for (int j = 0; j < 2; ++j) {
     cudaFree(c->tile_keys[j]);
     cudaFree(c->tile_vals[j]);
@@ -791,6 +834,53 @@ static int tile_order(lio_ctx* c, const float4* pts, int n, const StateArg& st, 
   return LIO_OK;
 }
 
+// Scan ordering through a captured graph: the keys kernel and the radix-sort passes cost ~45 us of device time but ~110 us
+// when launched one by one (the library queries kernel attributes on every call and the tiny passes leave the GPU waiting
+// for the host); as one graph launch the passes run back to back.  Graphs are cached per padded size (multiples of 8192).
+static int tile_order_graph(lio_ctx* c, int n, const double* state_host) {
+  int rc = tile_ensure(c, (uint32_t)n);
+  if (rc) return rc;
+  const int n_pad = std::min<int>((int)c->tile_cap, ((n + 8191) / 8192) * 8192);
+  if (!c->keys_args_host) {
+    LIO_CUDA(cudaHostAlloc(&c->keys_args_host, sizeof(KeysArgs), cudaHostAllocDefault));
+    LIO_CUDA(cudaMalloc(&c->keys_args_dev, sizeof(KeysArgs)));
+  }
+  cudaGraphExec_t exec = nullptr;
+  for (auto& g : c->sort_graphs)
+    if (g.first == n_pad) exec = (cudaGraphExec_t)g.second;
+  if (!exec) {
+    cudaGraph_t graph = nullptr;
+    LIO_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeRelaxed));
+    cudaMemcpyAsync(c->keys_args_dev, c->keys_args_host, sizeof(KeysArgs), cudaMemcpyHostToDevice, c->stream);
+    const int grid = std::max(1, std::min((n_pad + 255) / 256, c->n_sms * 8));
+    k_tile_keys_g<<<grid, 256, 0, c->stream>>>(c->map, c->body, (const KeysArgs*)c->keys_args_dev, n_pad, c->tile_keys[0], c->tile_vals[0]);
+    size_t bytes = c->tile_tmp_bytes;
+    const cudaError_t se = cub::DeviceRadixSort::SortPairs(c->tile_tmp, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0],
+                                                           c->tile_vals[1], n_pad, 0, kTileKeyBits, c->stream);
+    const cudaError_t ce = cudaStreamEndCapture(c->stream, &graph);
+    if (se != cudaSuccess || ce != cudaSuccess || !graph) {
+      if (graph) cudaGraphDestroy(graph);
+      cudaGetLastError();
+      c->sort_graph_ok = false;  // fall back to plain launches for the rest of this context's life
+      return LIO_E_STATE;
+    }
+    const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess || !exec) {
+      cudaGetLastError();
+      c->sort_graph_ok = false;
+      return LIO_E_STATE;
+    }
+    c->sort_graphs.emplace_back(n_pad, (void*)exec);
+  }
+  KeysArgs* a = (KeysArgs*)c->keys_args_host;
+  std::memcpy(a->s, state_host, sizeof(a->s));
+  a->n = n;
+  LIO_CUDA(cudaGraphLaunch(exec, c->stream));
+  c->launches += 1;  // our keys kernel (+ the library's sort passes)
+  return LIO_OK;
+}
+
 static int tile_grid(const lio_ctx* c, int n) {
   const int tiles = (n + 31) / 32;
   return std::max(1, std::min((tiles + kTileWarps - 1) / kTileWarps, c->n_sms * 8));
@@ -802,7 +892,8 @@ int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
   timer_begin(c, T_KNN);
   if (c->knn_mode == 1) {
     if (!c->order_valid) {  // once per scan: later calls move the points by centimetres, the order stays coherent
-      int rc = tile_order(c, c->body, n, st, true);
+      int rc = c->sort_graph_ok ? tile_order_graph(c, n, state_host) : LIO_E_STATE;
+      if (rc == LIO_E_STATE && !c->sort_graph_ok) rc = tile_order(c, c->body, n, st, true);
       if (rc) return rc;
       c->order_valid = true;
     }
@@ -890,21 +981,82 @@ int scan_plane_reduce(lio_ctx* c, const double* state_host, bool want_rows, bool
   return LIO_OK;
 }
 
+// map_incremental as one captured graph (13 small launches otherwise: the GPU waits for the host between them).  Cached per
+// (padded size, flg_ekf_inited); state and true size come from a device block refreshed by the graph's memcpy node.
+static int classify_insert_graph(lio_ctx* c, const double* state_host, int flg_ekf_inited) {
+  const int n = c->scan_n;
+  const int n_pad = std::min<int>((int)c->cfg.max_scan, ((n + 8191) / 8192) * 8192);
+  int rc = map_ensure_batch(c, (uint32_t)n_pad);  // allocations must not happen inside the capture
+  if (rc) return rc;
+  if (!c->map_args_host) {
+    LIO_CUDA(cudaHostAlloc(&c->map_args_host, sizeof(KeysArgs), cudaHostAllocDefault));
+    LIO_CUDA(cudaMalloc(&c->map_args_dev, sizeof(IekfCtl)));  // read through the IekfCtl view (x[36] first), n right after
+    LIO_CUDA(cudaMemsetAsync(c->map_args_dev, 0, sizeof(IekfCtl), c->stream));
+  }
+  const int key = n_pad * 2 + (flg_ekf_inited ? 1 : 0);
+  cudaGraphExec_t exec = nullptr;
+  for (auto& g : c->map_graphs)
+    if (g.first == key) exec = (cudaGraphExec_t)g.second;
+  if (!exec) {
+    const int blocks = (n_pad + 255) / 256;
+    const IekfCtl* st_view = (const IekfCtl*)c->map_args_dev;  // block_state<true> reads x[0..35] only
+    const int* n_ptr = (const int*)((const char*)c->map_args_dev + offsetof(KeysArgs, n));
+    cudaGraph_t graph = nullptr;
+    const bool was_timing = c->timing;
+    c->timing = false;  // no event records inside the capture
+    LIO_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeRelaxed));
+    cudaMemcpyAsync(c->map_args_dev, c->map_args_host, sizeof(KeysArgs), cudaMemcpyHostToDevice, c->stream);
+    StateArg unused{};
+    k_classify<true><<<blocks, 256, 0, c->stream>>>(c->body, n_pad, unused, c->nn, c->nn_cnt, flg_ekf_inited, c->cfg.filter_size_map,
+                                                    c->map.ctr, c->world, c->cls, c->blk_cnt, st_view, n_ptr);
+    k_scan_blocks<<<1, 1024, 0, c->stream>>>(c->blk_cnt, blocks, c->map.ctr);
+    k_scatter_lists<<<blocks, 256, 0, c->stream>>>(c->world, c->cls, n_pad, c->blk_cnt, c->list_add, c->list_nodown, n_ptr);
+    const int64_t l0 = c->launches;
+    int r1 = map_add_device(c, c->list_add, (uint32_t)n_pad, &c->map.ctr->list_add, true);
+    int r2 = map_add_device(c, c->list_nodown, (uint32_t)n_pad, &c->map.ctr->list_nodown, false);
+    c->map_graph_launches = 3 + (int)(c->launches - l0);
+    c->launches = l0;
+    const cudaError_t ce = cudaStreamEndCapture(c->stream, &graph);
+    c->timing = was_timing;
+    cudaError_t ie = cudaErrorUnknown;
+    if (r1 == LIO_OK && r2 == LIO_OK && ce == cudaSuccess && graph) ie = cudaGraphInstantiate(&exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (ie != cudaSuccess || !exec) {
+      cudaGetLastError();
+      c->map_graph_ok = false;
+      return LIO_E_STATE;
+    }
+    c->map_graphs.emplace_back(key, (void*)exec);
+  }
+  KeysArgs* a = (KeysArgs*)c->map_args_host;
+  std::memcpy(a->s, state_host, sizeof(a->s));
+  a->n = n;
+  timer_begin(c, T_INSERT);  // graph form: the whole map update is one timed region
+  LIO_CUDA(cudaGraphLaunch(exec, c->stream));
+  timer_end(c);
+  c->launches += c->map_graph_launches;
+  return LIO_OK;
+}
+
 int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inited, bool dev_loop) {
   const int n = c->scan_n;
   if (n <= 0) return LIO_OK;
+  if (!dev_loop && c->map_graph_ok) {
+    const int rc = classify_insert_graph(c, state_host, flg_ekf_inited);
+    if (rc != LIO_E_STATE || c->map_graph_ok) return rc;  // LIO_E_STATE with the flag cleared: capture failed, plain launches
+  }
   const int blocks = (n + 255) / 256;
   timer_begin(c, T_CLASSIFY);
   if (dev_loop) {
     StateArg unused{};
     k_classify<true><<<blocks, 256, 0, c->stream>>>(c->body, n, unused, c->nn, c->nn_cnt, flg_ekf_inited, c->cfg.filter_size_map, c->map.ctr,
-                                                    c->world, c->cls, c->blk_cnt, c->iekf_ctl);
+                                                    c->world, c->cls, c->blk_cnt, c->iekf_ctl, nullptr);
   } else {
     k_classify<false><<<blocks, 256, 0, c->stream>>>(c->body, n, make_state(state_host), c->nn, c->nn_cnt, flg_ekf_inited,
-                                                     c->cfg.filter_size_map, c->map.ctr, c->world, c->cls, c->blk_cnt, nullptr);
+                                                     c->cfg.filter_size_map, c->map.ctr, c->world, c->cls, c->blk_cnt, nullptr, nullptr);
   }
   k_scan_blocks<<<1, 1024, 0, c->stream>>>(c->blk_cnt, blocks, c->map.ctr);
-  k_scatter_lists<<<blocks, 256, 0, c->stream>>>(c->world, c->cls, n, c->blk_cnt, c->list_add, c->list_nodown);
+  k_scatter_lists<<<blocks, 256, 0, c->stream>>>(c->world, c->cls, n, c->blk_cnt, c->list_add, c->list_nodown, nullptr);
   c->launches += 3;
   timer_end(c);
   LIO_CUDA(cudaGetLastError());
