@@ -260,7 +260,7 @@ def run_ours(args, synth):
         clocks = clk.stop() if clk else None
         total_ms = sum(a.elapsed_time(b) for a, b in evs)
         launches = g.launch_count() - l0
-        kt = {k: g.timing_get(k) for k in ("knn", "plane_reduce", "insert", "classify")}
+        kt = {k: g.timing_get(k) for k in ("sort", "knn", "plane_reduce", "insert", "classify")}
         g.timing(False)
         return total_ms, calls, n_eff, launches, kt, clocks
 

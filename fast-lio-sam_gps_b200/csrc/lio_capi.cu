@@ -627,6 +627,7 @@ int lio_timing_get(lio_ctx* c, const char* name, double* mean_ms, int* launches)
   else if (!std::strcmp(name, "plane_reduce")) id = T_PLANE;
   else if (!std::strcmp(name, "insert")) id = T_INSERT;
   else if (!std::strcmp(name, "classify")) id = T_CLASSIFY;
+  else if (!std::strcmp(name, "sort")) id = T_SORT;
   if (id < 0) {
     set_error("unknown timer '%s'", name);
     return LIO_E_ARG;

@@ -31,7 +31,7 @@ struct HShareOut {
   unsigned long long pad;
 };
 
-enum TimerId { T_KNN = 0, T_PLANE, T_INSERT, T_CLASSIFY, T_COUNT };
+enum TimerId { T_KNN = 0, T_PLANE, T_INSERT, T_CLASSIFY, T_SORT, T_COUNT };
 
 struct EventPair {
   cudaEvent_t a, b;

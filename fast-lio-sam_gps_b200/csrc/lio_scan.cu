@@ -889,14 +889,16 @@ static int tile_grid(const lio_ctx* c, int n) {
 int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
   const int n = c->scan_n;
   const StateArg st = make_state(state_host);
+  if (c->knn_mode == 1 && !c->order_valid) {  // once per scan: later calls move the points by centimetres, the order stays coherent
+    timer_begin(c, T_SORT);
+    int rc = c->sort_graph_ok ? tile_order_graph(c, n, state_host) : LIO_E_STATE;
+    if (rc == LIO_E_STATE && !c->sort_graph_ok) rc = tile_order(c, c->body, n, st, true);
+    timer_end(c);
+    if (rc) return rc;
+    c->order_valid = true;
+  }
   timer_begin(c, T_KNN);
   if (c->knn_mode == 1) {
-    if (!c->order_valid) {  // once per scan: later calls move the points by centimetres, the order stays coherent
-      int rc = c->sort_graph_ok ? tile_order_graph(c, n, state_host) : LIO_E_STATE;
-      if (rc == LIO_E_STATE && !c->sort_graph_ok) rc = tile_order(c, c->body, n, st, true);
-      if (rc) return rc;
-      c->order_valid = true;
-    }
     uint32_t* ctr = c->tile_stats + 4 + 2 * (c->tile_flip & 1);
     uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
     c->tile_flip ^= 1;

@@ -216,6 +216,48 @@ def test_iekf_update_map_parity(pkg, orc, synth, small_world, mode):
 
 
 @pytest.mark.gpu
+def test_graphs_serve_changing_scan_sizes(pkg, orc, synth, small_world):
+    """The captured graphs (scan ordering, map_incremental) are cached per padded size and read the true size from device
+    memory: scans of different lengths through ONE context must match the oracle and a graph-free context bit for bit."""
+    w = small_world
+    P0 = synth.default_cov()
+    old = {k: os.environ.get(k) for k in ("LIO_SORT_GRAPH", "LIO_MAP_GRAPH")}
+    try:
+        g = pkg.LioContext(0.5, max_points=1 << 19, max_scan=1 << 16)
+        os.environ["LIO_SORT_GRAPH"] = os.environ["LIO_MAP_GRAPH"] = "0"
+        p = pkg.LioContext(0.5, max_points=1 << 19, max_scan=1 << 16)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    o = orc.OracleLio(0.5)
+    for c in (g, p, o):
+        c.map_build(w["map"])
+    n = len(w["scan"])
+    rng = np.random.default_rng(11)
+    for m in (n, n - 1000, 8192, 8193, 777, n):  # same bucket, other buckets, bucket edges, tiny, back again
+        scan = np.ascontiguousarray(w["scan"][rng.permutation(n)[:m]])
+        outs = []
+        for c in (g, p):
+            c.scan_upload(scan)
+            outs.append(c.iekf_update_map(w["start"], P0, True, trace=True))
+        o.scan_upload(scan)
+        os_, oP, oi = o.iekf_update(w["start"], P0, trace=True)
+        o.map_incremental(os_, True)
+        (gs, gP, gi), (ps, pP, pi) = outs
+        assert np.array_equal(gs, ps) and np.array_equal(gP, pP) and np.array_equal(gi["n_eff"], pi["n_eff"])
+        assert np.array_equal(gi["n_eff"], oi["n_eff"]) and np.abs(gs - os_).max() < STATE_TOL
+        gx, gid = g.map_export()
+        px, pid = p.map_export()
+        ox, oid = o.map_export()
+        assert np.array_equal(gid, oid) and np.array_equal(gx, ox) and np.array_equal(pid, oid) and np.array_equal(px, ox)
+    g.close()
+    p.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("mode", ["host", "dev"])
 def test_iekf_invalid_rounds_and_errors(pkg, orc, synth, small_world, mode):
     w = small_world
