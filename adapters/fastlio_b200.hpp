@@ -110,6 +110,27 @@ class FastLioB200 {
     return *n_eff >= 1;
   }
 
+  // The per-scan body of the main loop in one call: kf.update_iterated_dyn_share_modified(LASER_POINT_COV, ...) followed by
+  // map_incremental() at the updated state (lio_iekf_update_map).  P is the 23x23 covariance (row-major), limit = epsi.
+  // state_out receives the updated state in the LIO_STATE_DOUBLES layout (rotations as 3x3 row-major matrices): the caller
+  // writes it back with kf.change_x(...) the way it already does after set_extrinsic / init.
+  template <class State>
+  void update_and_map(const State &s, double *P23x23, double laser_point_cov, int max_iter, const double limit[23],
+                      double state_out[LIO_STATE_DOUBLES], bool flg_ekf_inited = true) {
+    pack_state(s, state_out);
+    check(lio_iekf_update_map(ctx_, state_out, P23x23, laser_point_cov, max_iter, limit, flg_ekf_inited ? 1 : 0, nullptr, nullptr, nullptr,
+                              nullptr),
+          "lio_iekf_update_map");
+  }
+  // ImuProcess::UndistortPcl's backward loop on the scan uploaded with set_scan(): t_ms[i] = points[i].curvature,
+  // pose6d = IMUpose flattened to LIO_POSE6D_DOUBLES per entry, end_state = imu_state after the last predict.
+  template <class State>
+  void undistort(const float *t_ms, const double *pose6d, int n_pose, const State &end_state) {
+    double st[LIO_STATE_DOUBLES];
+    pack_state(end_state, st);
+    check(lio_scan_undistort(ctx_, t_ms, pose6d, n_pose, st), "lio_scan_undistort");
+  }
+
   // map_incremental() at the updated state (flg_EKF_inited as in the reference)
   template <class State>
   void map_incremental(const State &s, bool flg_ekf_inited = true) {
