@@ -292,6 +292,12 @@ def run_ours(args, synth):
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
+        traffic = None  # DRAM bytes per search from the committed ncu --set full capture (profiles/traffic.json)
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["iekf_knn"]
+            traffic = {"bytes_per_launch": tr["bytes_per_launch"], "source": tr["source"]} if tr and args.n_scan == N_SCAN and args.n_map == N_MAP else None
+        except Exception:
+            pass
         knn_ms, knn_n = kt["knn"]
         algo_bytes = ALGO_BYTES_PER_POINT * args.n_scan
         achieved = algo_bytes / (knn_ms * 1e-3) / 1e9 if knn_ms > 0 else 0.0
@@ -307,7 +313,8 @@ def run_ours(args, synth):
                     "d2h_bytes_per_step": int(round((36 + 529) * 8 + e_calls / args.steps * (36 * 8 + 8) + 16))},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k_knn_tile + k_knn_left (body->world + exact k=5 NN; Morton sort on the first call of a scan)", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic["bytes_per_launch"] if traffic else None,
+                         "traffic_source": traffic["source"] if traffic else None,
                          "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": knn_ms, "launches_timed": knn_n,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650"},
             "kernel_ms": {k: {"mean_ms": v[0], "launches": v[1]} for k, v in kt.items()},

@@ -16,6 +16,12 @@ def shard_pairs(n_pairs, rank, world):
     return importlib.import_module("fast-lio-sam_gps_b200.loop").shard_pairs(n_pairs, rank, world)
 
 
+def shard_pair_indices(n_pairs, rank, world):
+    import importlib
+
+    return importlib.import_module("fast-lio-sam_gps_b200.loop").shard_pair_indices(n_pairs, rank, world)
+
+
 def make_loop_workload(synth, n_pairs=256, n_pass=100, n_az=1800, submap_range=12, seed=None):
     """Out-and-back drive; pair = (pass-2 keyframe, its pass-1 counterpart shifted by -1/0/+1).  The drift of pass 2 is
     ~1 m / 3 deg."""
@@ -105,8 +111,8 @@ def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmu
     import torch.distributed as dist
 
     w = make_loop_workload(synth, n_pairs=n_pairs, n_pass=n_pass, n_az=n_az, submap_range=submap_range)
-    lo, hi = shard_pairs(n_pairs, rank, world)
-    mine = w["pairs"][lo:hi]
+    idx = shard_pair_indices(n_pairs, rank, world)  # two contiguous blocks per rank (see loop.shard_pair_indices)
+    mine = [w["pairs"][i] for i in idx]
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -116,27 +122,34 @@ def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmu
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)  # device-timed, max over ranks
         gathered = [None] * world
-        dist.all_gather_object(gathered, [(r["valid"], r["converged"], r["iterations"], float(r["score"])) for r in res])  # host gather
+        dist.all_gather_object(gathered, [(i, r["valid"], r["converged"], r["iterations"], float(r["score"])) for i, r in zip(idx, res)])  # host gather
     ms_max = float(t.item())
     if rank != 0:
         return None
-    flat = [x for part in gathered for x in part]
+    flat = sorted(x for part in gathered for x in part) if world > 1 else res  # back in pair order
     nn_ms, nn_n = kt["nn"]
     sc_ms, sc_n = kt["score"]
     q = stats["nn_queries"]
     peak = _peak()
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")))["loop_icp_nn"]
+    except Exception:
+        pass
     achieved = ICP_ALGO_BYTES * q / ((nn_ms + sc_ms) * 1e-3) / 1e9 if nn_ms + sc_ms > 0 else 0.0
     out = {
         "metric": "loop-ICP pairs/s", "value": n_pairs / (ms_max * 1e-3), "unit": "pairs/s", "n_gpus": world, "ms_per_batch": ms_max,
-        "pairs": n_pairs, "pairs_rank0": hi - lo, "scaling": "strong", "submap_keyframes_per_side": 2 * submap_range + 1,
+        "pairs": n_pairs, "pairs_rank0": len(idx), "scaling": "strong", "submap_keyframes_per_side": 2 * submap_range + 1,
         "points_per_keyframe": int(np.mean([len(c) for c in w["clouds"]])), "voxel_res": LEAF, "max_corr_dist": RADIUS * 1.5,
-        "results_gathered": len(flat),
+        "results_gathered": len(flat), "valid_total": int(sum(bool(x[1]) for x in flat)) if world > 1 else int(sum(bool(r["valid"]) for r in res)),
+        "sharding": "2 contiguous blocks per rank, dealt there and back (loop.shard_pair_indices)",
         "rank0": {"valid": int(sum(bool(r["valid"]) for r in res)), "converged": int(sum(bool(r["converged"]) for r in res)),
                   "mean_iterations": stats["iterations"] / max(len(res), 1), "mean_src_points": stats["src_points"] / max(len(res), 1),
                   "gpu_launches_per_batch": launches,
                   "kernel_ms": {k: {"total_ms": v[0], "launches": v[1]} for k, v in kt.items()}},
         "roofline": {"bound": "hbm", "kernel": "k_icp_nn (transform + exact 1-NN, all pairs per launch)", "achieved": achieved,
-                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic["bytes_per_launch"] if traffic else None,
+                     "traffic_source": traffic["source"] if traffic else None,
                      "algorithmic_bytes": ICP_ALGO_BYTES * q, "kernel_ms_total": nn_ms + sc_ms, "launches_timed": nn_n + sc_n},
     }
     if cpu_pairs > 0:

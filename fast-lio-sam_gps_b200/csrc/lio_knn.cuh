@@ -294,4 +294,120 @@ __device__ void knn_search(const MapView& m, const Group<G>& g, float qx, float 
   }
 }
 
+// ------------------------------------------------------------------------------------------------ warp per query
+// One query per warp, 128 cells probed per step (four rounds of lane-parallel hash probes in flight), the hit buckets
+// read 16 at a time (one 128-byte line per 8 lanes, four loads in flight per lane).  Serves the queries the tile kernel
+// defers: those are few (a few % of a scan) but deep — a query with fewer than five neighbours inside max_d2 has to see
+// every cell within sqrt(max_d2), 343 of them at 1 m cells — so the sequential chain per query is what bounds the
+// launch, and a warp cuts it 4x against the 8-lane group.  Same exact result as knn_search<G>.
+struct WarpList {
+  uint32_t b[128];  // hit buckets of the current step
+  uint32_t n[128];  // their overflow bucket (kNone: none)
+};
+
+__device__ __forceinline__ void warp_scan_step(const MapView& m, WarpList& wl, int lane, int cx, int cy, int cz, int ring, int idx0,
+                                               float qx, float qy, float qz, float tau, uint32_t max_bits, TopList& L) {
+  const float h = m.cell_size;
+  const int side = 2 * ring + 1, total = side * side * side;
+  const unsigned lt = (1u << lane) - 1u;
+  unsigned long long key4[4];
+  uint32_t slot4[4];
+  uint4 raw4[4];
+  bool want4[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int idx = idx0 + u * 32 + lane;
+    const int dz = idx / (side * side) - ring, dy = (idx / side) % side - ring, dx = idx % side - ring;
+    bool want = idx < total && (ring == 1 || max(max(abs(dx), abs(dy)), abs(dz)) == ring);
+    if (want && ring > 1) want = cell_box_d2(qx, qy, qz, cx + dx, cy + dy, cz + dz, h) * 0.9999f <= tau;
+    want4[u] = want;
+    key4[u] = pack3(cx + dx, cy + dy, cz + dz);
+    slot4[u] = hash64(key4[u]) & m.mask;
+    raw4[u] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, kNone, kNone);
+    if (want) raw4[u] = __ldg(reinterpret_cast<const uint4*>(m.table + slot4[u]));
+  }
+  int nb = 0;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    unsigned long long ek = ((unsigned long long)raw4[u].y << 32) | raw4[u].x;
+    while (want4[u] && ek != key4[u] && ek != kEmptyKey) {  // linear probing past a collision
+      slot4[u] = (slot4[u] + 1) & m.mask;
+      raw4[u] = __ldg(reinterpret_cast<const uint4*>(m.table + slot4[u]));
+      ek = ((unsigned long long)raw4[u].y << 32) | raw4[u].x;
+    }
+    const bool hit = want4[u] && ek == key4[u];
+    const unsigned hb = __ballot_sync(0xFFFFFFFFu, hit);
+    if (hit) {
+      const int pos = nb + __popc(hb & lt);
+      wl.b[pos] = raw4[u].z;
+      wl.n[pos] = raw4[u].w;
+    }
+    nb += __popc(hb);
+  }
+  __syncwarp();
+  const int sub = lane >> 3, sl = lane & 7;
+  for (int b0 = 0; b0 < nb; b0 += 16) {
+    float4 p[4];
+    uint32_t bk[4], ov[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int wi = b0 + 4 * u + sub;
+      bk[u] = ov[u] = kNone;
+      if (wi < nb) {
+        bk[u] = wl.b[wi];
+        ov[u] = wl.n[wi];
+        p[u] = __ldg(m.slots + (size_t)bk[u] * kSlots + sl);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (bk[u] != kNone) {
+        const uint32_t id = __float_as_uint(p[u].w);
+        const float d2 = sqdist3(qx, qy, qz, p[u].x, p[u].y, p[u].z);
+        if (id != kEmptyId && d2 <= __uint_as_float(max_bits)) L.insert(key64(d2, id), bk[u] * kSlots + sl);
+      }
+      uint32_t b = ov[u];  // overflow buckets of the cell: rare, walked by the 8-lane sub-group that read its head
+      while (__any_sync(0xFFFFFFFFu, b != kNone)) {
+        if (b != kNone) {
+          const float4 q = __ldg(m.slots + (size_t)b * kSlots + sl);
+          const uint32_t id = __float_as_uint(q.w);
+          const float d2 = sqdist3(qx, qy, qz, q.x, q.y, q.z);
+          if (id != kEmptyId && d2 <= __uint_as_float(max_bits)) L.insert(key64(d2, id), b * kSlots + sl);
+          b = __ldg(m.next + b);
+        }
+      }
+    }
+  }
+  __syncwarp();  // the list is rewritten by the next step
+}
+
+// Result valid in lanes < cnt of the warp: key (d2 bits << 32 | id), ref (slot index).
+__device__ void knn_search_warp(const MapView& m, WarpList& wl, float qx, float qy, float qz, float max_d2, unsigned long long& okey,
+                                uint32_t& oref, int& cnt) {
+  const Group<32> g;
+  const int lane = g.gl;
+  const float h = m.cell_size;
+  const int cx = vox_of(qx, m.ds) >> m.cell_shift, cy = vox_of(qy, m.ds) >> m.cell_shift, cz = vox_of(qz, m.ds) >> m.cell_shift;
+  const uint32_t max_bits = __float_as_uint(max_d2);
+  TopList L;
+  L.clear();
+  warp_scan_step(m, wl, lane, cx, cy, cz, 1, 0, qx, qy, qz, max_d2, max_bits, L);
+  merge_top<32>(g, L, okey, oref, cnt);
+  const float fx = qx - (float)cx * h, fy = qy - (float)cy * h, fz = qz - (float)cz * h;  // offset inside the centre cell
+  const float lo = fminf(fminf(fx, fy), fz), hi = fminf(fminf(h - fx, h - fy), h - fz);
+  const float edge = fmaxf(fminf(lo, hi), 0.f);  // distance to the nearest face of the centre cell
+  const int max_ring = (int)ceilf(sqrtf(max_d2) / h) + 1;
+  for (int ring = 2; ring <= max_ring; ++ring) {
+    const float reach = ((float)(ring - 1) * h + edge) * 0.9999f;  // everything within `reach` of the query has been seen
+    const unsigned long long k5 = g.shfl(okey, kK - 1);
+    const float tau = (cnt == kK) ? __uint_as_float((uint32_t)(k5 >> 32)) : max_d2;
+    if (tau < reach * reach) break;
+    L.clear();
+    if (lane < cnt) L.insert(okey, oref);  // re-seed the private lists with the current answer
+    const int side = 2 * ring + 1, total = side * side * side;
+    for (int idx0 = 0; idx0 < total; idx0 += 128) warp_scan_step(m, wl, lane, cx, cy, cz, ring, idx0, qx, qy, qz, tau, max_bits, L);
+    merge_top<32>(g, L, okey, oref, cnt);
+  }
+}
+
 }  // namespace lio

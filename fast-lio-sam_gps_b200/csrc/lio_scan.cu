@@ -195,18 +195,20 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
   }
 }
 
-// Per-query search (lio_knn.cuh, 8 lanes per query) of the queries the tile kernel deferred.
+// Per-query search (lio_knn.cuh, one warp per query: knn_search_warp) of the queries the tile kernel deferred.
+constexpr int kLeftGridMult = 6;  // blocks per SM of k_knn_left
 template <bool XFORM, bool DEV>
-__global__ void __launch_bounds__(kKnnBlock) k_knn_left(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
+__global__ void __launch_bounds__(kKnnBlock, 6) k_knn_left(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
                                                         StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
                                                         float* __restrict__ nn_d2, int* __restrict__ nn_cnt, uint32_t* __restrict__ ctr,
                                                         uint32_t* __restrict__ ctr_next, uint32_t* __restrict__ stats,
                                                         const IekfCtl* __restrict__ ctl) {
   __shared__ StateArg s_st;
-  const Group<8> g;
-  const int groups_per_block = kKnnBlock / 8;
-  const int gid = blockIdx.x * groups_per_block + (threadIdx.x / 8);
-  const int gstride = gridDim.x * groups_per_block;
+  __shared__ WarpList s_wl[kKnnBlock / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warps_per_block = kKnnBlock / 32;
+  const int wid = blockIdx.x * warps_per_block + warp;
+  const int wstride = gridDim.x * warps_per_block;
   const bool skip = DEV && (ctl->finished || !ctl->converge);  // the tile kernel did not run: ctr is still zero
   const int n_left = skip ? 0 : (int)ctr[1];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -217,7 +219,7 @@ __global__ void __launch_bounds__(kKnnBlock) k_knn_left(MapView m, const float4*
   const StateArg& st = block_state<DEV>(st_param, ctl, s_st);
   const float4 pad = make_float4(0.f, 0.f, 0.f, __uint_as_float(kEmptyId));
   const float inf = __int_as_float(0x7f800000);
-  for (int j = gid; j < n_left; j += gstride) {
+  for (int j = wid; j < n_left; j += wstride) {
     const uint32_t i = __ldg(left + j);
     const float4 b = __ldg(pts + i);
     float qx = b.x, qy = b.y, qz = b.z;
@@ -225,14 +227,14 @@ __global__ void __launch_bounds__(kKnnBlock) k_knn_left(MapView m, const float4*
     unsigned long long key;
     uint32_t ref;
     int cnt;
-    knn_search<8>(m, g, qx, qy, qz, max_d2, key, ref, cnt);
+    knn_search_warp(m, s_wl[warp], qx, qy, qz, max_d2, key, ref, cnt);
     cnt = min(cnt, k);
-    if (g.gl < k) {
-      const bool have = g.gl < cnt;
-      nn[(size_t)i * k + g.gl] = have ? __ldg(m.slots + ref) : pad;
-      if (nn_d2) nn_d2[(size_t)i * k + g.gl] = have ? __uint_as_float((uint32_t)(key >> 32)) : inf;
+    if (lane < k) {
+      const bool have = lane < cnt;
+      nn[(size_t)i * k + lane] = have ? __ldg(m.slots + ref) : pad;
+      if (nn_d2) nn_d2[(size_t)i * k + lane] = have ? __uint_as_float((uint32_t)(key >> 32)) : inf;
     }
-    if (g.gl == 0) nn_cnt[i] = cnt;
+    if (lane == 0) nn_cnt[i] = cnt;
   }
 }
 
@@ -905,12 +907,12 @@ int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
     if (dev_loop) {
       k_knn_tile<true, true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
                                                                                   c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], c->iekf_ctl, c->tile_stats);
-      k_knn_left<true, true><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
+      k_knn_left<true, true><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
                                                                          c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, c->iekf_ctl);
     } else {
       k_knn_tile<true, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
                                                                                    c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats);
-      k_knn_left<true, false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
+      k_knn_left<true, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
                                                                           c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, nullptr);
     }
     c->launches += 1;
@@ -938,7 +940,7 @@ int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float
     c->tile_flip ^= 1;
     k_knn_tile<false, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, q_dev, c->tile_vals[1], n, st, k, max_d2, out_nn,
                                                                                   out_d2, out_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats);
-    k_knn_left<false, false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
+    k_knn_left<false, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
                                                                          ctr, ctr_next, c->tile_stats, nullptr);
     c->launches += 1;
   } else {

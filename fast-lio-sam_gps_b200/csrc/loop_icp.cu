@@ -185,12 +185,21 @@ __device__ __forceinline__ void scan_leaf(const float4* __restrict__ pts, uint32
 __device__ __forceinline__ bool visit(float d, float bd) { return d < INFINITY && d * 0.9999f <= bd; }
 
 // Exact nearest neighbour of q in tree `tr`; bi = original index in the target cloud (kPadIdx: none), bp = its point.
+// `seed` (original index of a target point, or -1) starts the search from that point's distance: the correspondence of the
+// previous ICP iteration moves by millimetres, so its distance prunes nearly every subtree the cold search would still
+// enter.  The result is the same minimum of (distance, index) over the whole target either way.
 __device__ void nn_search(const TreeDev& tr, const Node2* __restrict__ nodes, const float4* __restrict__ tree_pts, float qx, float qy,
-                          float qz, float& bd, uint32_t& bi, float4& bp) {
+                          float qz, float& bd, uint32_t& bi, float4& bp, int seed = -1, const float4* __restrict__ target = nullptr) {
   bd = INFINITY;
   bi = kPadIdx;
   bp = make_float4(0.f, 0.f, 0.f, 0.f);
   if (tr.n == 0 || !(isfinite(qx) && isfinite(qy) && isfinite(qz))) return;
+  if (seed >= 0) {
+    const float4 s = __ldg(target + seed);
+    bd = sqd3(qx, qy, qz, s.x, s.y, s.z);
+    bi = (uint32_t)seed;
+    bp = s;
+  }
   const Node2* nd = nodes + tr.node_off;
   const float4* pts = tree_pts + tr.pts_off;
   const uint32_t first_leaf_parent = tr.nleaf_pad >> 1;
@@ -279,7 +288,9 @@ __global__ void __launch_bounds__(kBlock) k_icp_nn(PairDev* __restrict__ pairs, 
     float bd;
     uint32_t bi;
     float4 bp;
-    nn_search(trees[pr.dst_job], nodes, tree_pts, x, y, z, bd, bi, bp);
+    const TreeDev& tr = trees[pr.dst_job];
+    const int seed = pr.iters > 0 ? match[ci] : -1;  // written by the previous iteration of this pair
+    nn_search(tr, nodes, tree_pts, x, y, z, bd, bi, bp, seed, vox + tr.src_off);
     if (MODE == 0) {
       const bool ok = bi != kPadIdx && !((double)bd > max_d2);
       match[ci] = ok ? (int)bi : -1;

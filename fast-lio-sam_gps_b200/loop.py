@@ -105,6 +105,18 @@ def shard_pairs(n_pairs, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def shard_pair_indices(n_pairs, rank, world):
+    """Pair indices owned by `rank`: the list is cut into 2*world contiguous blocks and rank r takes blocks r and
+    2*world-1-r (dealt there and back).  Contiguous blocks keep the pairs of neighbouring query keyframes together (they
+    share submaps, so each is built once per rank); the mirrored second block cancels a trend in ICP iteration count along
+    the list (drift grows along a drive), which with one contiguous slice per rank left the slowest rank 25 % over the mean."""
+    out = []
+    for b in (rank, 2 * world - 1 - rank):
+        lo, hi = shard_pairs(n_pairs, b, 2 * world)
+        out.extend(range(lo, hi))
+    return out
+
+
 class LoopClosure:
     """Mirror of the reference's LoopClosure: keyframes live on the device, candidate pairs are verified in batches.
 

@@ -103,7 +103,12 @@ def _f64(a):
 
 
 def max_threads():
-    return lib().orc_max_threads()
+    """Host threads the CPU legs use: every core this process may run on.  Not omp_get_max_threads(): torchrun exports
+    OMP_NUM_THREADS=1 to its workers, which would silently time the OpenMP oracle on one core."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or lib().orc_max_threads())
 
 
 class OracleLio:

@@ -23,14 +23,14 @@ def _worker(rank, world, port, q):
     from oracle import orc
 
     w = lb.make_loop_workload(synth, n_pairs=5, n_pass=8, n_az=120, submap_range=2)
-    lo, hi = lb.shard_pairs(len(w["pairs"]), rank, world)
-    res, _ = lb.cpu_loop(orc, w, w["pairs"][lo:hi], 0.3, 1.5, 52.5, 1)
-    mine = [(lo + i, r["iterations"], bool(r["valid"]), float(r["score"]), r["T"].tobytes()) for i, r in enumerate(res)]
+    idx = lb.shard_pair_indices(len(w["pairs"]), rank, world)
+    res, _ = lb.cpu_loop(orc, w, [w["pairs"][i] for i in idx], 0.3, 1.5, 52.5, 1)
+    mine = [(i, r["iterations"], bool(r["valid"]), float(r["score"]), r["T"].tobytes()) for i, r in zip(idx, res)]
     gathered = [None] * world
     dist.all_gather_object(gathered, mine)
     dist.barrier()
     if rank == 0:
-        q.put([x for part in gathered for x in part])
+        q.put(sorted(x for part in gathered for x in part))  # back in pair order, as loop_section does
     dist.destroy_process_group()
 
 
@@ -43,6 +43,21 @@ def test_shard_pairs_partition():
             assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))
             sizes = [hi - lo for lo, hi in cuts]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_shard_pair_indices_partition():
+    """Two blocks per rank, dealt there and back: a partition of the list, sizes within 2, and the positions a rank owns
+    average to the middle of the list (what cancels a linear cost trend)."""
+    lb = importlib.import_module("bench_loop")
+    for n in (0, 1, 5, 256, 257):
+        for world in (1, 2, 3, 8):
+            parts = [lb.shard_pair_indices(n, r, world) for r in range(world)]
+            assert sorted(i for p in parts for i in p) == list(range(n))
+            sizes = [len(p) for p in parts]
+            assert max(sizes) - min(sizes) <= 2
+            if n % (2 * world) == 0 and n:
+                assert all(abs(np.mean(p) - (n - 1) / 2) < 1e-9 for p in parts)
+    assert lb.shard_pair_indices(256, 0, 8) == list(range(0, 16)) + list(range(240, 256))
 
 
 @pytest.mark.timeout(300)
