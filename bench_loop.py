@@ -148,7 +148,7 @@ def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmu
                   "gpu_launches_per_batch": launches,
                   "kernel_ms": {k: {"total_ms": v[0], "launches": v[1]} for k, v in kt.items()}},
         "roofline": {"bound": "hbm", "kernel": "k_icp_nn (transform + exact 1-NN, all pairs per launch)", "achieved": achieved,
-                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic["bytes_per_launch"] if traffic else None,
+                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": int(traffic["bytes_per_query"] * q) if traffic else None,
                      "traffic_source": traffic["source"] if traffic else None,
                      "algorithmic_bytes": ICP_ALGO_BYTES * q, "kernel_ms_total": nn_ms + sc_ms, "launches_timed": nn_n + sc_n},
     }

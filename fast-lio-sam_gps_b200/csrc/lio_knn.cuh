@@ -305,17 +305,22 @@ struct WarpList {
   uint32_t n[128];  // their overflow bucket (kNone: none)
 };
 
-__device__ __forceinline__ void warp_scan_step(const MapView& m, WarpList& wl, int lane, int cx, int cy, int cz, int ring, int idx0,
+// RING_T > 0: the ring is a compile-time constant (cell index -> offset is then multiply-shift instead of three integer
+// divisions, which were a third of the instructions of a deep query); RING_T == 0: run-time ring.  ROUNDS <= 4 probe
+// rounds of 32 cells per step.
+template <int RING_T, int ROUNDS>
+__device__ __forceinline__ void warp_scan_step(const MapView& m, WarpList& wl, int lane, int cx, int cy, int cz, int ring_rt, int idx0,
                                                float qx, float qy, float qz, float tau, uint32_t max_bits, TopList& L) {
   const float h = m.cell_size;
+  const int ring = RING_T ? RING_T : ring_rt;
   const int side = 2 * ring + 1, total = side * side * side;
   const unsigned lt = (1u << lane) - 1u;
-  unsigned long long key4[4];
-  uint32_t slot4[4];
-  uint4 raw4[4];
-  bool want4[4];
+  unsigned long long key4[ROUNDS];
+  uint32_t slot4[ROUNDS];
+  uint4 raw4[ROUNDS];
+  bool want4[ROUNDS];
 #pragma unroll
-  for (int u = 0; u < 4; ++u) {
+  for (int u = 0; u < ROUNDS; ++u) {
     const int idx = idx0 + u * 32 + lane;
     const int dz = idx / (side * side) - ring, dy = (idx / side) % side - ring, dx = idx % side - ring;
     bool want = idx < total && (ring == 1 || max(max(abs(dx), abs(dy)), abs(dz)) == ring);
@@ -328,7 +333,7 @@ __device__ __forceinline__ void warp_scan_step(const MapView& m, WarpList& wl, i
   }
   int nb = 0;
 #pragma unroll
-  for (int u = 0; u < 4; ++u) {
+  for (int u = 0; u < ROUNDS; ++u) {
     unsigned long long ek = ((unsigned long long)raw4[u].y << 32) | raw4[u].x;
     while (want4[u] && ek != key4[u] && ek != kEmptyKey) {  // linear probing past a collision
       slot4[u] = (slot4[u] + 1) & m.mask;
@@ -391,7 +396,7 @@ __device__ void knn_search_warp(const MapView& m, WarpList& wl, float qx, float 
   const uint32_t max_bits = __float_as_uint(max_d2);
   TopList L;
   L.clear();
-  warp_scan_step(m, wl, lane, cx, cy, cz, 1, 0, qx, qy, qz, max_d2, max_bits, L);
+  warp_scan_step<1, 1>(m, wl, lane, cx, cy, cz, 1, 0, qx, qy, qz, max_d2, max_bits, L);
   merge_top<32>(g, L, okey, oref, cnt);
   const float fx = qx - (float)cx * h, fy = qy - (float)cy * h, fz = qz - (float)cz * h;  // offset inside the centre cell
   const float lo = fminf(fminf(fx, fy), fz), hi = fminf(fminf(h - fx, h - fy), h - fz);
@@ -404,8 +409,16 @@ __device__ void knn_search_warp(const MapView& m, WarpList& wl, float qx, float 
     if (tau < reach * reach) break;
     L.clear();
     if (lane < cnt) L.insert(okey, oref);  // re-seed the private lists with the current answer
-    const int side = 2 * ring + 1, total = side * side * side;
-    for (int idx0 = 0; idx0 < total; idx0 += 128) warp_scan_step(m, wl, lane, cx, cy, cz, ring, idx0, qx, qy, qz, tau, max_bits, L);
+    if (ring == 2) {
+      warp_scan_step<2, 4>(m, wl, lane, cx, cy, cz, 2, 0, qx, qy, qz, tau, max_bits, L);  // 125 cells
+    } else if (ring == 3) {
+#pragma unroll 1
+      for (int idx0 = 0; idx0 < 343; idx0 += 128) warp_scan_step<3, 4>(m, wl, lane, cx, cy, cz, 3, idx0, qx, qy, qz, tau, max_bits, L);
+    } else {
+      const int side = 2 * ring + 1, total = side * side * side;
+#pragma unroll 1
+      for (int idx0 = 0; idx0 < total; idx0 += 128) warp_scan_step<0, 4>(m, wl, lane, cx, cy, cz, ring, idx0, qx, qy, qz, tau, max_bits, L);
+    }
     merge_top<32>(g, L, okey, oref, cnt);
   }
 }

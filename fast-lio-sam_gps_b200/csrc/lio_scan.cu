@@ -196,9 +196,9 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
 }
 
 // Per-query search (lio_knn.cuh, one warp per query: knn_search_warp) of the queries the tile kernel deferred.
-constexpr int kLeftGridMult = 6;  // blocks per SM of k_knn_left
+constexpr int kLeftGridMult = 4;  // blocks per SM of k_knn_left
 template <bool XFORM, bool DEV>
-__global__ void __launch_bounds__(kKnnBlock, 6) k_knn_left(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
+__global__ void __launch_bounds__(kKnnBlock, 4) k_knn_left(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
                                                         StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
                                                         float* __restrict__ nn_d2, int* __restrict__ nn_cnt, uint32_t* __restrict__ ctr,
                                                         uint32_t* __restrict__ ctr_next, uint32_t* __restrict__ stats,

@@ -77,39 +77,7 @@ __global__ void __launch_bounds__(256) k_submap(const SegDev* __restrict__ segs,
     }
     finite = isfinite(o.x) && isfinite(o.y) && isfinite(o.z);
   }
-  // warp-aggregated box update when the whole warp works on one job
-  const unsigned full = 0xFFFFFFFFu;
-  const int job0 = __shfl_sync(full, job, 0);
-  const bool uniform = __all_sync(full, job == job0 || job < 0) && job0 >= 0;
-  if (uniform) {
-    uint32_t lo[3] = {finite ? f2ord(o.x) : 0xFFFFFFFFu, finite ? f2ord(o.y) : 0xFFFFFFFFu, finite ? f2ord(o.z) : 0xFFFFFFFFu};
-    uint32_t hi[3] = {finite ? f2ord(o.x) : 0u, finite ? f2ord(o.y) : 0u, finite ? f2ord(o.z) : 0u};
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-#pragma unroll
-      for (int a = 0; a < 3; ++a) {
-        lo[a] = min(lo[a], __shfl_xor_sync(full, lo[a], off));
-        hi[a] = max(hi[a], __shfl_xor_sync(full, hi[a], off));
-      }
-    }
-    const unsigned nf = __popc(__ballot_sync(full, finite));
-    if ((threadIdx.x & 31) == 0 && nf) {
-#pragma unroll
-      for (int a = 0; a < 3; ++a) {
-        atomicMin(&acc[job0].lo[a], lo[a]);
-        atomicMax(&acc[job0].hi[a], hi[a]);
-      }
-      atomicAdd(&acc[job0].n_finite, nf);
-    }
-  } else if (finite && job >= 0) {
-    atomicMin(&acc[job].lo[0], f2ord(o.x));
-    atomicMin(&acc[job].lo[1], f2ord(o.y));
-    atomicMin(&acc[job].lo[2], f2ord(o.z));
-    atomicMax(&acc[job].hi[0], f2ord(o.x));
-    atomicMax(&acc[job].hi[1], f2ord(o.y));
-    atomicMax(&acc[job].hi[2], f2ord(o.z));
-    atomicAdd(&acc[job].n_finite, 1u);
-  }
+  block_box_update(acc, job, finite, o.x, o.y, o.z);
 }
 
 // PCL VoxelGrid::applyFilter prologue, one thread for all jobs (n_jobs is small); also the sorted offsets

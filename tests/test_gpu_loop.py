@@ -53,6 +53,33 @@ def test_transform_pcd_bit_exact(closers, orc, synth, drive):
     assert len(g.transform_pcd(np.zeros((0, 4), np.float32), T)) == 0
 
 
+def test_pose_pcd_ctor_stores_lidar_frame(closers, orc, synth, drive):
+    """pose_pcd.hpp:38-39: the published world-frame cloud is re-expressed in the LiDAR frame with pose^-1; and the loop
+    factor built from a verified pair (fast_lio_sam.cpp:699-717) closes the chain pose_from * measured = pose_to."""
+    import importlib
+
+    tj = importlib.import_module("fast-lio-sam_gps_b200.trajectory")
+    g, _ = closers
+    clouds, est = drive[0], drive[1]
+    world = g.transform_pcd(clouds[2], est[2])
+    kf = tj.PosePcd.from_world_cloud(g, world, est[2], 12.5, 2)
+    inv = np.linalg.inv(np.asarray(est[2], np.float64))
+    inv[3] = [0, 0, 0, 1]
+    assert np.allclose(kf.pcd, orc.transform_pcd(world, np.ascontiguousarray(inv)), atol=1e-5)
+    assert np.allclose(kf.pcd[:, :3], clouds[2][:, :3], atol=2e-4) and np.array_equal(kf.pcd[:, 3], clouds[2][:, 3])
+    assert kf.idx == 2 and kf.timestamp == 12.5 and np.array_equal(kf.pose_corrected_eig, kf.pose_eig)
+    K = len(clouds)
+    closest = g.fetch_closest_keyframe_idx(K - 1)
+    assert closest >= 0
+    r = g.perform_loop_closure(K - 1, closest)
+    f = tj.loop_factor(r, est[K - 1], est[closest], K - 1, closest)
+    if r["valid"]:
+        pose_from = np.asarray(r["T"], np.float64).reshape(4, 4) @ np.asarray(est[K - 1], np.float64)
+        assert np.allclose(pose_from @ f["measured"], est[f["key_to"]], atol=1e-9) and np.all(f["variances"] == r["score"])
+    else:
+        assert f is None
+
+
 def test_voxelize_bit_exact(closers, orc, drive):
     g, _ = closers
     rng = np.random.default_rng(1)
