@@ -104,6 +104,7 @@ int loop_ctx_create(const loop_config* cfg, loop_ctx** out) {
   if (!c) return LOOP_E_ARG;
   c->cfg = *cfg;
   c->n_sms = prop.multiProcessorCount;
+  if (const char* e = getenv("LOOP_TREE_ORDER")) c->tree_order = (e[0] == 'm' || e[0] == '0') ? 0 : 1;
   c->prm.max_d2 = cfg->max_corr_dist * cfg->max_corr_dist;
   c->prm.trans_eps = cfg->transformation_epsilon;
   c->prm.fit_eps = cfg->euclidean_fitness_epsilon;

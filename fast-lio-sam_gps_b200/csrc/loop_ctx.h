@@ -123,6 +123,7 @@ struct loop_ctx {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   int n_sms = 0;
+  int tree_order = 1;  // 0: Morton, 1: Hilbert order of the target trees (LOOP_TREE_ORDER=morton|hilbert)
 
   // keyframe store
   loopb::DevBuf<float4> kf_pts;

@@ -70,10 +70,38 @@ __device__ __forceinline__ uint32_t spread10(uint32_t v) {
   return v;
 }
 
-// sort key (tree << 32 | 30-bit Morton code inside the tree's box); only the ORDER matters, not exactness
+// 30-bit Hilbert index of a 10-bit-per-axis cell (Skilling's axes-to-transpose form).  Index ranges of a Hilbert curve are
+// spatially connected, so the halves of an index-balanced tree get tighter, less overlapping boxes than with Morton
+// order, whose ranges jump across the cube at every octant boundary.
+__device__ __forceinline__ uint32_t hilbert30(uint32_t x, uint32_t y, uint32_t z) {
+  uint32_t X[3] = {x, y, z};
+  const uint32_t M = 1u << 9;
+  for (uint32_t Q = M; Q > 1; Q >>= 1) {
+    const uint32_t P = Q - 1;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      if (X[i] & Q) {
+        X[0] ^= P;
+      } else {
+        const uint32_t t = (X[0] ^ X[i]) & P;
+        X[0] ^= t;
+        X[i] ^= t;
+      }
+    }
+  }
+  X[1] ^= X[0];
+  X[2] ^= X[1];
+  uint32_t t = 0;
+  for (uint32_t Q = M; Q > 1; Q >>= 1)
+    if (X[2] & Q) t ^= Q - 1;
+  X[0] ^= t; X[1] ^= t; X[2] ^= t;
+  return (spread10(X[0]) << 2) | (spread10(X[1]) << 1) | spread10(X[2]);
+}
+
+// sort key (tree << 32 | 30-bit space-filling-curve index inside the tree's box); only the ORDER matters, not exactness
 __global__ void __launch_bounds__(kBlock) k_tree_keys(const TreeDev* __restrict__ trees, const uint32_t* __restrict__ cmp_off, int n_trees,
                                                       uint32_t n_total, const float4* __restrict__ vox, const BoxAcc* __restrict__ acc,
-                                                      unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+                                                      unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals, int hilbert) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_total) return;
   const int t = find_tree(cmp_off, n_trees, i);
@@ -88,7 +116,8 @@ __global__ void __launch_bounds__(kBlock) k_tree_keys(const TreeDev* __restrict_
     const uint32_t qx = (uint32_t)fminf(fmaxf((p.x - lo[0]) * sc, 0.f), 1023.f);
     const uint32_t qy = (uint32_t)fminf(fmaxf((p.y - lo[1]) * sc, 0.f), 1023.f);
     const uint32_t qz = (uint32_t)fminf(fmaxf((p.z - lo[2]) * sc, 0.f), 1023.f);
-    code = spread10(qx) | (spread10(qy) << 1) | (spread10(qz) << 2);
+    code = hilbert ? hilbert30(qx, qy, qz) : (spread10(qx) | (spread10(qy) << 1) | (spread10(qz) << 2));
+    if (code == 0x3FFFFFFFu) code = 0x3FFFFFFEu;  // the all-ones code is reserved for non-finite points
   }
   keys[i] = ((unsigned long long)(uint32_t)t << 32) | code;
   vals[i] = l;
@@ -642,7 +671,7 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs) {
     BoxAcc* acc = reinterpret_cast<BoxAcc*>(c->cub_tmp.p);
     k_tree_box_init<<<grid_of(nt, 128), 128, 0, s>>>(acc, nt);
     k_tree_box<<<grid_of(cmp, kBlock), kBlock, 0, s>>>(c->trees.p, cmp_off, nt, cmp, c->vox.p, acc);
-    k_tree_keys<<<grid_of(cmp, kBlock), kBlock, 0, s>>>(c->trees.p, cmp_off, nt, cmp, c->vox.p, acc, c->keys_a.p, c->vals_a.p);
+    k_tree_keys<<<grid_of(cmp, kBlock), kBlock, 0, s>>>(c->trees.p, cmp_off, nt, cmp, c->vox.p, acc, c->keys_a.p, c->vals_a.p, c->tree_order);
     size_t bytes = c->cub_tmp.cap;
     LOOP_CUDA(cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, bytes, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)cmp, 0, 32 + bits, s));
     c->launches += 4;
