@@ -29,6 +29,7 @@ constexpr int kStageUnroll = 4;     // bucket loads in flight per lane while sta
 // run-time tuning knobs (defaults = the constants above; LIO_TILE_MAXSUB / LIO_TILE_MAXE at context creation)
 __device__ __constant__ int c_tile_max_sub = kTileMaxSub;
 __device__ __constant__ int c_tile_max_e = kTileMaxE;
+__device__ __constant__ int c_tile_hilbert = 1;  // LIO_TILE_ORDER=morton|hilbert
 
 struct __align__(16) TileSmem {
   float4 pts[kTileCap];
@@ -80,8 +81,38 @@ __device__ __forceinline__ uint32_t spread8(uint32_t x) {
   x = (x | (x << 2)) & 0x00249249u;
   return x;
 }
+// 24-bit Hilbert index of an 8-bit-per-axis cell (Skilling's axes-to-transpose form).  Consecutive index ranges of the
+// Hilbert curve are spatially connected, so the 32 queries of a tile stay in neighbouring cells where a Morton range
+// jumps across the cube at every octant boundary (tiles the search then has to split or defer).
+__device__ __forceinline__ uint32_t hilbert24(uint32_t x, uint32_t y, uint32_t z) {
+  uint32_t X[3] = {x & 0xffu, y & 0xffu, z & 0xffu};
+  const uint32_t M = 1u << 7;
+#pragma unroll
+  for (uint32_t Q = M; Q > 1; Q >>= 1) {
+    const uint32_t P = Q - 1;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      if (X[i] & Q) {
+        X[0] ^= P;
+      } else {
+        const uint32_t t = (X[0] ^ X[i]) & P;
+        X[0] ^= t;
+        X[i] ^= t;
+      }
+    }
+  }
+  X[1] ^= X[0];
+  X[2] ^= X[1];
+  uint32_t t = 0;
+#pragma unroll
+  for (uint32_t Q = M; Q > 1; Q >>= 1)
+    if (X[2] & Q) t ^= Q - 1;
+  X[0] ^= t; X[1] ^= t; X[2] ^= t;
+  return (spread8(X[0]) << 2) | (spread8(X[1]) << 1) | spread8(X[2]);
+}
 __device__ __forceinline__ uint32_t tile_key(const MapView& m, float x, float y, float z) {
   const int cx = vox_of(x, m.ds) >> m.cell_shift, cy = vox_of(y, m.ds) >> m.cell_shift, cz = vox_of(z, m.ds) >> m.cell_shift;
+  if (c_tile_hilbert) return hilbert24((uint32_t)cx, (uint32_t)cy, (uint32_t)cz);
   return spread8((uint32_t)cx) | (spread8((uint32_t)cy) << 1) | (spread8((uint32_t)cz) << 2);
 }
 

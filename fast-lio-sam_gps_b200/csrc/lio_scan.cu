@@ -716,6 +716,9 @@ int scan_alloc(lio_ctx* c) {
       const int me = e ? std::max(1, std::min(8, atoi(e))) : kTileMaxE;
       LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_max_sub, &sub, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
       LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_max_e, &me, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
+      e = getenv("LIO_TILE_ORDER");
+      const int hil = (e && (e[0] == 'm' || e[0] == '0')) ? 0 : 1;
+      LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_hilbert, &hil, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
       LIO_CUDA(cudaStreamSynchronize(c->stream));
     }
     e = getenv("LIO_SORT_GRAPH");

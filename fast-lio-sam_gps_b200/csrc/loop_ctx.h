@@ -80,7 +80,9 @@ struct GridDev {
 struct PairDev {
   uint32_t src_off, src_n;  // voxelised source cloud
   uint32_t dst_job;         // index of the target cloud's tree
-  uint32_t cur_off;         // offset of the pair's working arrays (cur, match, md2)
+  uint32_t cur_off;         // offset of the pair's working arrays (cur, match, md2), indexed by Hilbert position
+  uint32_t src_pts_off;     // the source cloud in Hilbert order (tree point buffer: xyz + original index bits, leaf padded)
+  uint32_t src_pad_n;       // its padded length (pad entries carry kPadIdx and are skipped)
   // accumulators (exact fixed point)
   long long ss[3], sd[3], cov[9], mse_fix, cnt;
   long long score_fix, score_n;
@@ -88,6 +90,7 @@ struct PairDev {
   double prev_mse;
   int similar, iters, state, converged, active;
   int pad;
+  int pad2[2];
 };
 
 struct TreeDev {

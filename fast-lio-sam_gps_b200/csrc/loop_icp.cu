@@ -297,12 +297,17 @@ __global__ void __launch_bounds__(kBlock) k_icp_nn(PairDev* __restrict__ pairs, 
   __syncthreads();
   const uint32_t l = first + threadIdx.x;
   long long v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (l < pr.src_n) {
-    const size_t ci = (size_t)pr.cur_off + l;
+  // the source points are visited in Hilbert order (the warp's 32 queries walk the same part of the target tree: fewer
+  // divergent traversal steps, node lines shared through L1); every sum below is an exact fixed-point sum, so the
+  // visiting order does not change a bit of the result
+  const float4 s = (l < pr.src_pad_n) ? __ldg(tree_pts + pr.src_pts_off + l) : make_float4(0.f, 0.f, 0.f, __uint_as_float(kPadIdx));
+  const size_t ci = (size_t)pr.cur_off + l;
+  if (__float_as_uint(s.w) == kPadIdx) {
+    if (MODE == 0 && l < pr.src_pad_n && pr.iters == 0) match[ci] = -1;
+  } else {
     float x, y, z;
     if (MODE == 0) {
       if (pr.iters == 0) {
-        const float4 s = __ldg(vox + pr.src_off + l);
         x = s.x; y = s.y; z = s.z;
       } else {
         const float4 c = cur[ci];
@@ -310,7 +315,6 @@ __global__ void __launch_bounds__(kBlock) k_icp_nn(PairDev* __restrict__ pairs, 
       }
       cur[ci] = make_float4(x, y, z, 0.f);
     } else {
-      const float4 s = __ldg(vox + pr.src_off + l);
       tf_f_sse(s_T, s.x, s.y, s.z, x, y, z);
     }
     float bd;
@@ -361,7 +365,7 @@ __global__ void __launch_bounds__(kBlock) k_icp_cov(PairDev* __restrict__ pairs,
   }
   const uint32_t l = first + threadIdx.x;
   long long v[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-  if (l < pr.src_n) {
+  if (l < pr.src_pad_n) {
     const size_t ci = (size_t)pr.cur_off + l;
     const int m = match[ci];
     if (m >= 0) {
@@ -702,6 +706,11 @@ int run_icp(loop_ctx* c, const std::vector<PairHost>& ph, double score_thr, loop
       tree_of_job[p.dst_job] = (int)tree_jobs.size();
       tree_jobs.push_back(p.dst_job);
     }
+  for (const PairHost& p : ph)  // the source clouds go through the same ordering pass: their points are visited in Hilbert order
+    if (tree_of_job[p.src_job] < 0) {
+      tree_of_job[p.src_job] = (int)tree_jobs.size();
+      tree_jobs.push_back(p.src_job);
+    }
   int rc = build_trees(c, tree_jobs);
   if (rc) return rc;
 
@@ -714,15 +723,18 @@ int run_icp(loop_ctx* c, const std::vector<PairHost>& ph, double score_thr, loop
     pr.src_off = g.vox_off;
     pr.src_n = g.vox_n;
     pr.dst_job = (uint32_t)tree_of_job[ph[p].dst_job];
+    const TreeDev& stree = c->trees_host[tree_of_job[ph[p].src_job]];
+    pr.src_pts_off = stree.pts_off;
+    pr.src_pad_n = stree.nleaf * kLeafPts;
     pr.cur_off = (uint32_t)cur_total;
     for (int k = 0; k < 16; ++k) pr.Tr[k] = pr.Tfinal[k] = (k % 5 == 0) ? 1.f : 0.f;
     pr.prev_mse = DBL_MAX;
     pr.active = 1;
-    for (uint32_t b = 0; b < pr.src_n; b += kBlock) {
+    for (uint32_t b = 0; b < pr.src_pad_n; b += kBlock) {
       b2p.push_back((uint32_t)p);
       b2p.push_back(b);
     }
-    cur_total += pr.src_n;
+    cur_total += pr.src_pad_n;
   }
   if (cur_total >= 0xFFFFFFFFull) {
     lio::set_error("batch chunk holds %llu source points (limit 2^32-1)", (unsigned long long)cur_total);
@@ -802,8 +814,19 @@ int fetch_aligned(loop_ctx* c, int pair, float* out, int cap, int* n_out) {
 int fetch_corr(loop_ctx* c, int pair, int* out) {
   const PairDev& pr = c->pairs_host[pair];
   if (!pr.src_n) return LOOP_OK;
-  LOOP_CUDA(cudaMemcpyAsync(out, c->match.p + pr.cur_off, sizeof(int) * (size_t)pr.src_n, cudaMemcpyDeviceToHost, c->stream));
+  // match[] is indexed by Hilbert position: put it back in the source cloud's own order (points that are not in the
+  // ordering, i.e. non-finite ones, have no correspondence)
+  std::vector<int> m(pr.src_pad_n);
+  std::vector<float4> pts(pr.src_pad_n);
+  LOOP_CUDA(cudaMemcpyAsync(m.data(), c->match.p + pr.cur_off, sizeof(int) * m.size(), cudaMemcpyDeviceToHost, c->stream));
+  LOOP_CUDA(cudaMemcpyAsync(pts.data(), c->tree_pts.p + pr.src_pts_off, sizeof(float4) * pts.size(), cudaMemcpyDeviceToHost, c->stream));
   LOOP_CUDA(cudaStreamSynchronize(c->stream));
+  for (uint32_t i = 0; i < pr.src_n; ++i) out[i] = -1;
+  for (uint32_t l = 0; l < pr.src_pad_n; ++l) {
+    uint32_t orig;
+    std::memcpy(&orig, &pts[l].w, sizeof(orig));
+    if (orig != kPadIdx && orig < pr.src_n) out[orig] = m[l];
+  }
   return LOOP_OK;
 }
 
