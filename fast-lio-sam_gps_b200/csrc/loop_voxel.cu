@@ -81,10 +81,14 @@ __global__ void __launch_bounds__(256) k_submap(const SegDev* __restrict__ segs,
 }
 
 // PCL VoxelGrid::applyFilter prologue, one thread for all jobs (n_jobs is small); also the sorted offsets
-__global__ void k_grid(const BoxAcc* __restrict__ acc, GridDev* __restrict__ grids, int n_jobs, float leaf) {
+// idx_bits_out: bits needed by the largest linear voxel index of any job (the sort key is job << idx_bits | index, so the
+// radix passes cover only bits that can differ)
+__global__ void k_grid(const BoxAcc* __restrict__ acc, GridDev* __restrict__ grids, const JobDev* __restrict__ jobs, int n_jobs, float leaf,
+                       uint32_t* __restrict__ idx_bits_out) {
   if (blockIdx.x || threadIdx.x) return;
   const float inv = 1.0f / leaf;
   uint32_t run = 0;
+  unsigned long long max_cells = 2;
   for (int j = 0; j < n_jobs; ++j) {
     GridDev g;
     g.n_finite = acc[j].n_finite;
@@ -103,24 +107,30 @@ __global__ void k_grid(const BoxAcc* __restrict__ acc, GridDev* __restrict__ gri
     }
     if (d[0] * d[1] * d[2] > 2147483647LL) {
       g.overflow = 1;
+      max_cells = max(max_cells, (unsigned long long)jobs[j].raw_n);
     } else {
       g.mul1 = (int)d[0];
       g.mul2 = (int)(d[0] * d[1]);
+      max_cells = max(max_cells, (unsigned long long)(d[0] * d[1] * d[2]));
     }
     grids[j] = g;
   }
+  uint32_t bits = 1;
+  while (bits < 32 && (1ull << bits) < max_cells) ++bits;
+  *idx_bits_out = bits;
 }
 
+template <typename KeyT>
 __global__ void __launch_bounds__(256) k_keys(const float4* __restrict__ raw, uint32_t n_raw, const JobDev* __restrict__ jobs, int n_jobs,
-                                              const GridDev* __restrict__ grids, float leaf, uint32_t sentinel,
-                                              unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+                                              const GridDev* __restrict__ grids, float leaf, uint32_t sentinel, int shift,
+                                              KeyT* __restrict__ keys, uint32_t* __restrict__ vals) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_raw) return;
   const float4 p = raw[i];
   const int j = find_job(jobs, n_jobs, i);
-  unsigned long long key;
+  KeyT key;
   if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) {
-    key = (unsigned long long)sentinel << 32;
+    key = (KeyT)sentinel << shift;
   } else {
     const GridDev& g = grids[j];
     uint32_t lin;
@@ -133,27 +143,29 @@ __global__ void __launch_bounds__(256) k_keys(const float4* __restrict__ raw, ui
       const int i2 = (int)(floorf(p.z * inv) - (float)g.minb[2]);
       lin = (uint32_t)(i0 + i1 * g.mul1 + i2 * g.mul2);
     }
-    key = ((unsigned long long)(uint32_t)j << 32) | lin;
+    key = ((KeyT)(uint32_t)j << shift) | (KeyT)lin;
   }
   keys[i] = key;
   vals[i] = i;
 }
 
-__global__ void __launch_bounds__(256) k_heads(const unsigned long long* __restrict__ keys, uint32_t n, uint32_t sentinel,
+template <typename KeyT>
+__global__ void __launch_bounds__(256) k_heads(const KeyT* __restrict__ keys, uint32_t n, uint32_t sentinel, int shift,
                                                uint32_t* __restrict__ flags) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const unsigned long long k = keys[i];
-  const bool live = (uint32_t)(k >> 32) != sentinel;
+  const KeyT k = keys[i];
+  const bool live = (uint32_t)(k >> shift) != sentinel;
   flags[i] = (live && (i == 0 || keys[i - 1] != k)) ? 1u : 0u;
 }
 
-__global__ void __launch_bounds__(256) k_centroids(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals,
+template <typename KeyT>
+__global__ void __launch_bounds__(256) k_centroids(const KeyT* __restrict__ keys, const uint32_t* __restrict__ vals,
                                                    const uint32_t* __restrict__ flags, const uint32_t* __restrict__ slot, uint32_t n,
                                                    const float4* __restrict__ raw, float4* __restrict__ vox) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n || !flags[i]) return;
-  const unsigned long long k = keys[i];
+  const KeyT k = keys[i];
   float sx = 0.f, sy = 0.f, sz = 0.f, si = 0.f;
   uint32_t j = i;
   do {
@@ -204,7 +216,7 @@ static int voxelize_raw(loop_ctx* c, const std::vector<JobDev>& jd, const SegDev
   LOOP_CUDA(cudaMemcpyAsync(c->jobs.p, jd.data(), sizeof(JobDev) * n_jobs, cudaMemcpyHostToDevice, s));
   // BoxAcc cells live at the head of the cub scratch buffer for the duration of the box pass
   DevBuf<unsigned char>& tmp = c->cub_tmp;
-  if ((rc = tmp.ensure(sizeof(BoxAcc) * (size_t)n_jobs))) return rc;
+  if ((rc = tmp.ensure(sizeof(BoxAcc) * ((size_t)n_jobs + 1)))) return rc;  // + one cell for k_grid's scalar when there are no points
   BoxAcc* acc = reinterpret_cast<BoxAcc*>(tmp.p);
   k_box_init<<<grid_of(n_jobs, 128), 128, 0, s>>>(acc, n_jobs);
   c->launches += 1;
@@ -218,29 +230,41 @@ static int voxelize_raw(loop_ctx* c, const std::vector<JobDev>& jd, const SegDev
     c->launches += 1;
   }
   tbegin(c, LT_VOXEL);
-  k_grid<<<1, 32, 0, s>>>(acc, c->grids.p, n_jobs, leaf);
+  // head_scan[0] carries the voxel-index width to the host (the buffer is not in use before the scan below)
+  k_grid<<<1, 32, 0, s>>>(acc, c->grids.p, c->jobs.p, n_jobs, leaf, n_raw ? c->head_scan.p : reinterpret_cast<uint32_t*>(acc + n_jobs));
   c->launches += 1;
   if (n_raw) {
     int bits = 1;
     while ((1u << bits) - 1u < (uint32_t)n_jobs) ++bits;  // sentinel = 2^bits - 1 >= n_jobs
     const uint32_t sentinel = (1u << bits) - 1u;
-    k_keys<<<grid_of(n_raw, 256), 256, 0, s>>>(c->raw.p, n_raw, c->jobs.p, n_jobs, c->grids.p, leaf, sentinel, c->keys_a.p, c->vals_a.p);
-    c->launches += 1;
+    uint32_t shift = 32;
+    LOOP_CUDA(cudaMemcpyAsync(&shift, c->head_scan.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    LOOP_CUDA(cudaStreamSynchronize(s));  // also orders k_grid (last reader of the BoxAcc cells) before a scratch reallocation
+    const int end_bit = (int)shift + bits;
+    const bool narrow = end_bit <= 32;  // job and voxel index fit one 32-bit key: 8 B instead of 12 B per element and pass
+    uint32_t* ka32 = reinterpret_cast<uint32_t*>(c->keys_a.p);
+    uint32_t* kb32 = reinterpret_cast<uint32_t*>(c->keys_b.p);
     size_t need = 0, need2 = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, need, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)n_raw, 0, 32 + bits, s);
+    if (narrow) cub::DeviceRadixSort::SortPairs(nullptr, need, ka32, kb32, c->vals_a.p, c->vals_b.p, (int)n_raw, 0, end_bit, s);
+    else cub::DeviceRadixSort::SortPairs(nullptr, need, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)n_raw, 0, end_bit, s);
     cub::DeviceScan::ExclusiveSum(nullptr, need2, c->vals_a.p, c->head_scan.p, (int)n_raw, s);
     need = std::max(need, need2);
-    // the BoxAcc cells were consumed by k_grid (stream order), so the scratch buffer may be reallocated now
-    if (need > tmp.cap) {
-      LOOP_CUDA(cudaStreamSynchronize(s));
-      if ((rc = tmp.ensure(need))) return rc;
-    }
+    if ((rc = tmp.ensure(need))) return rc;
     size_t bytes = tmp.cap;
-    LOOP_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, bytes, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)n_raw, 0, 32 + bits, s));
-    k_heads<<<grid_of(n_raw, 256), 256, 0, s>>>(c->keys_b.p, n_raw, sentinel, c->vals_a.p);
+    if (narrow) {
+      k_keys<uint32_t><<<grid_of(n_raw, 256), 256, 0, s>>>(c->raw.p, n_raw, c->jobs.p, n_jobs, c->grids.p, leaf, sentinel, (int)shift, ka32, c->vals_a.p);
+      LOOP_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, bytes, ka32, kb32, c->vals_a.p, c->vals_b.p, (int)n_raw, 0, end_bit, s));
+      k_heads<uint32_t><<<grid_of(n_raw, 256), 256, 0, s>>>(kb32, n_raw, sentinel, (int)shift, c->vals_a.p);
+    } else {
+      k_keys<unsigned long long><<<grid_of(n_raw, 256), 256, 0, s>>>(c->raw.p, n_raw, c->jobs.p, n_jobs, c->grids.p, leaf, sentinel, (int)shift,
+                                                                      c->keys_a.p, c->vals_a.p);
+      LOOP_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, bytes, c->keys_a.p, c->keys_b.p, c->vals_a.p, c->vals_b.p, (int)n_raw, 0, end_bit, s));
+      k_heads<unsigned long long><<<grid_of(n_raw, 256), 256, 0, s>>>(c->keys_b.p, n_raw, sentinel, (int)shift, c->vals_a.p);
+    }
     bytes = tmp.cap;
     LOOP_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, bytes, c->vals_a.p, c->head_scan.p, (int)n_raw, s));
-    k_centroids<<<grid_of(n_raw, 256), 256, 0, s>>>(c->keys_b.p, c->vals_b.p, c->vals_a.p, c->head_scan.p, n_raw, c->raw.p, c->vox.p);
+    if (narrow) k_centroids<uint32_t><<<grid_of(n_raw, 256), 256, 0, s>>>(kb32, c->vals_b.p, c->vals_a.p, c->head_scan.p, n_raw, c->raw.p, c->vox.p);
+    else k_centroids<unsigned long long><<<grid_of(n_raw, 256), 256, 0, s>>>(c->keys_b.p, c->vals_b.p, c->vals_a.p, c->head_scan.p, n_raw, c->raw.p, c->vox.p);
     k_job_ranges<<<1, 32, 0, s>>>(c->grids.p, n_jobs, c->vals_a.p, c->head_scan.p, n_raw);
     c->launches += 8;  // keys/heads/centroids/ranges + the library sort and scan passes (counted as one each)
   }
