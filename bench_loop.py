@@ -119,7 +119,10 @@ def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmu
     res, ms, kt, stats, launches = gpu_loop(loop_mod, w, mine, device=local_rank, steps=steps, warmup=warmup, stream=stream)
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     gathered = [res]
+    per_rank = [(ms, stats["iterations"] / max(len(res), 1))]
     if world > 1:
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, (ms, stats["iterations"] / max(len(res), 1)))  # where the imbalance sits
         dist.all_reduce(t, op=dist.ReduceOp.MAX)  # device-timed, max over ranks
         gathered = [None] * world
         dist.all_gather_object(gathered, [(i, r["valid"], r["converged"], r["iterations"], float(r["score"])) for i, r in zip(idx, res)])  # host gather
@@ -143,6 +146,7 @@ def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmu
         "points_per_keyframe": int(np.mean([len(c) for c in w["clouds"]])), "voxel_res": LEAF, "max_corr_dist": RADIUS * 1.5,
         "results_gathered": len(flat), "valid_total": int(sum(bool(x[1]) for x in flat)) if world > 1 else int(sum(bool(r["valid"]) for r in res)),
         "sharding": "2 contiguous blocks per rank, dealt there and back (loop.shard_pair_indices)",
+        "per_rank_ms": [round(float(a), 3) for a, _ in per_rank], "per_rank_mean_iterations": [round(float(b), 3) for _, b in per_rank],
         "rank0": {"valid": int(sum(bool(r["valid"]) for r in res)), "converged": int(sum(bool(r["converged"]) for r in res)),
                   "mean_iterations": stats["iterations"] / max(len(res), 1), "mean_src_points": stats["src_points"] / max(len(res), 1),
                   "gpu_launches_per_batch": launches,
