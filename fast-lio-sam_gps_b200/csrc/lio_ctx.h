@@ -98,6 +98,7 @@ struct lio_ctx {
   uint32_t* tile_stats = nullptr;  // [0] queries that went to the per-query fallback (debug/bench counter)
   int tile_flip = 0;             // which counter pair the next search uses
   int knn_mode = 1;              // 1 tile (default), 0 per-query groups (LIO_KNN_MODE=group)
+  int batch_left_warp = 0;  // LIO_BATCH_LEFT=warp: generic query batches also use the warp-per-query leftover kernel
   double* state_dev = nullptr;  // 36 doubles
   double* partials = nullptr;   // reduction partials
   int partial_blocks = 0;

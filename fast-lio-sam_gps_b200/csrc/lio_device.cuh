@@ -54,6 +54,11 @@ struct MapView {
   float ds;        // filter_size_map
   int cell_shift;  // log2(cell_mult)
   float cell_size; // ds * cell_mult
+  // coarse occupancy: one 64-bit word per 4x4x4 block of cells, addressed by a hash of the block's coordinates.  Bit
+  // (x&3) | (y&3)<<2 | (z&3)<<4 is set when the cell was ever created.  Blocks that collide share a word, so a set bit
+  // means "may exist" (the hash table is still probed), a clear bit means "does not exist" - never the other way round.
+  unsigned long long* occ;
+  uint32_t occ_mask;  // words - 1
 };
 
 #ifdef __CUDACC__
@@ -80,6 +85,11 @@ __device__ __forceinline__ uint32_t hash64(unsigned long long k) {
   k ^= k >> 33;
   return (uint32_t)k;
 }
+
+__device__ __forceinline__ uint32_t occ_word_of(const MapView& m, int bx, int by, int bz) {
+  return hash64(pack3(bx, by, bz) ^ 0x9E3779B97F4A7C15ull) & m.occ_mask;
+}
+__device__ __forceinline__ int occ_bit_of(int cx, int cy, int cz) { return (cx & 3) | ((cy & 3) << 2) | ((cz & 3) << 4); }
 
 // read-only lookup; returns the entry (key == kEmptyKey when the cell does not exist)
 __device__ __forceinline__ HashEntry table_find(const MapView& m, unsigned long long key) {

@@ -301,19 +301,21 @@ __device__ void knn_search(const MapView& m, const Group<G>& g, float qx, float 
 // every cell within sqrt(max_d2), 343 of them at 1 m cells — so the sequential chain per query is what bounds the
 // launch, and a warp cuts it 4x against the 8-lane group.  Same exact result as knn_search<G>.
 struct WarpList {
-  uint32_t b[128];  // hit buckets of the current step
-  uint32_t n[128];  // their overflow bucket (kNone: none)
+  uint32_t b[128];      // hit buckets of the current step
+  uint32_t n[128];      // their overflow bucket (kNone: none)
+  uint32_t cells[256];  // rings 2-3: offsets (dx+8 | dy+8 << 8 | dz+8 << 16) of the cells worth probing (occupancy words)
 };
 
 // RING_T > 0: the ring is a compile-time constant (cell index -> offset is then multiply-shift instead of three integer
 // divisions, which were a third of the instructions of a deep query); RING_T == 0: run-time ring.  ROUNDS <= 4 probe
 // rounds of 32 cells per step.
-template <int RING_T, int ROUNDS>
+// LIST: the cells come from wl.cells[0, ring_rt) (already filtered by shell, box distance and occupancy) instead of the cube.
+template <int RING_T, int ROUNDS, bool LIST = false>
 __device__ __forceinline__ void warp_scan_step(const MapView& m, WarpList& wl, int lane, int cx, int cy, int cz, int ring_rt, int idx0,
                                                float qx, float qy, float qz, float tau, uint32_t max_bits, TopList& L) {
   const float h = m.cell_size;
   const int ring = RING_T ? RING_T : ring_rt;
-  const int side = 2 * ring + 1, total = side * side * side;
+  const int side = 2 * ring + 1, total = LIST ? ring_rt : side * side * side;
   const unsigned lt = (1u << lane) - 1u;
   unsigned long long key4[ROUNDS];
   uint32_t slot4[ROUNDS];
@@ -322,9 +324,17 @@ __device__ __forceinline__ void warp_scan_step(const MapView& m, WarpList& wl, i
 #pragma unroll
   for (int u = 0; u < ROUNDS; ++u) {
     const int idx = idx0 + u * 32 + lane;
-    const int dz = idx / (side * side) - ring, dy = (idx / side) % side - ring, dx = idx % side - ring;
-    bool want = idx < total && (ring == 1 || max(max(abs(dx), abs(dy)), abs(dz)) == ring);
-    if (want && ring > 1) want = cell_box_d2(qx, qy, qz, cx + dx, cy + dy, cz + dz, h) * 0.9999f <= tau;
+    int dx, dy, dz;
+    bool want;
+    if (LIST) {
+      want = idx < total;
+      const uint32_t pk = want ? wl.cells[idx] : 0x080808u;
+      dx = (int)(pk & 0xffu) - 8, dy = (int)((pk >> 8) & 0xffu) - 8, dz = (int)((pk >> 16) & 0xffu) - 8;
+    } else {
+      dz = idx / (side * side) - ring, dy = (idx / side) % side - ring, dx = idx % side - ring;
+      want = idx < total && (ring == 1 || max(max(abs(dx), abs(dy)), abs(dz)) == ring);
+      if (want && ring > 1) want = cell_box_d2(qx, qy, qz, cx + dx, cy + dy, cz + dz, h) * 0.9999f <= tau;
+    }
     want4[u] = want;
     key4[u] = pack3(cx + dx, cy + dy, cz + dz);
     slot4[u] = hash64(key4[u]) & m.mask;
@@ -386,6 +396,52 @@ __device__ __forceinline__ void warp_scan_step(const MapView& m, WarpList& wl, i
   __syncwarp();  // the list is rewritten by the next step
 }
 
+// 64-bit mask of the cells of block (bx,by,bz) (4x4x4 cells) that lie within Chebyshev distance r of cell (cx,cy,cz)
+__device__ __forceinline__ unsigned long long occ_cube_mask(int bx, int by, int bz, int cx, int cy, int cz, int r) {
+  unsigned xm = 0, ym = 0, zm = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    xm |= (abs(bx * 4 + k - cx) <= r) ? (1u << k) : 0u;
+    ym |= (abs(by * 4 + k - cy) <= r) ? (1u << k) : 0u;
+    zm |= (abs(bz * 4 + k - cz) <= r) ? (1u << k) : 0u;
+  }
+  const unsigned long long mx = (unsigned long long)xm * 0x1111111111111111ull;
+  unsigned long long my = 0, mz = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    my |= ((ym >> k) & 1u) ? (0x000F000F000F000Full << (4 * k)) : 0ull;
+    mz |= ((zm >> k) & 1u) ? (0xFFFFull << (16 * k)) : 0ull;
+  }
+  return mx & my & mz;
+}
+
+// Rings 2 and 3 through the occupancy words: lane l < 27 holds the word of one 4x4x4 block around the query (`occ`, block
+// coordinates bx,by,bz).  The cells of shell `ring` that were ever created and whose box is within tau go to wl.cells;
+// returns their number.  In the sparse far-range regions where the deferred queries live this list has a handful of
+// entries where the cube enumeration probed 98 / 218 mostly empty cells.
+__device__ __forceinline__ int occ_ring_list(const MapView& m, WarpList& wl, int lane, unsigned long long occ, int bx, int by, int bz, int cx,
+                                             int cy, int cz, int ring, float qx, float qy, float qz, float tau) {
+  const unsigned lt = (1u << lane) - 1u;
+  unsigned long long bits = occ ? (occ & occ_cube_mask(bx, by, bz, cx, cy, cz, ring) & ~occ_cube_mask(bx, by, bz, cx, cy, cz, ring - 1)) : 0ull;
+  int n = 0;
+  while (__any_sync(0xFFFFFFFFu, bits != 0ull)) {
+    bool want = false;
+    uint32_t pk = 0;
+    if (bits) {
+      const int b = __ffsll((long long)bits) - 1;
+      bits &= bits - 1;
+      const int dx = bx * 4 + (b & 3) - cx, dy = by * 4 + ((b >> 2) & 3) - cy, dz = bz * 4 + (b >> 4) - cz;
+      want = cell_box_d2(qx, qy, qz, cx + dx, cy + dy, cz + dz, m.cell_size) * 0.9999f <= tau;
+      pk = (uint32_t)(dx + 8) | ((uint32_t)(dy + 8) << 8) | ((uint32_t)(dz + 8) << 16);
+    }
+    const unsigned wb = __ballot_sync(0xFFFFFFFFu, want);
+    if (want) wl.cells[n + __popc(wb & lt)] = pk;
+    n += __popc(wb);
+  }
+  __syncwarp();
+  return n;
+}
+
 // Result valid in lanes < cnt of the warp: key (d2 bits << 32 | id), ref (slot index).
 __device__ void knn_search_warp(const MapView& m, WarpList& wl, float qx, float qy, float qz, float max_d2, unsigned long long& okey,
                                 uint32_t& oref, int& cnt) {
@@ -402,6 +458,10 @@ __device__ void knn_search_warp(const MapView& m, WarpList& wl, float qx, float 
   const float lo = fminf(fminf(fx, fy), fz), hi = fminf(fminf(h - fx, h - fy), h - fz);
   const float edge = fmaxf(fminf(lo, hi), 0.f);  // distance to the nearest face of the centre cell
   const int max_ring = (int)ceilf(sqrtf(max_d2) / h) + 1;
+  // occupancy words of the (at most 3x3x3) blocks that cover rings 2 and 3, fetched on first use
+  unsigned long long occ = 0;
+  int obx = 0, oby = 0, obz = 0;
+  bool occ_loaded = false;
   for (int ring = 2; ring <= max_ring; ++ring) {
     const float reach = ((float)(ring - 1) * h + edge) * 0.9999f;  // everything within `reach` of the query has been seen
     const unsigned long long k5 = g.shfl(okey, kK - 1);
@@ -409,11 +469,19 @@ __device__ void knn_search_warp(const MapView& m, WarpList& wl, float qx, float 
     if (tau < reach * reach) break;
     L.clear();
     if (lane < cnt) L.insert(okey, oref);  // re-seed the private lists with the current answer
-    if (ring == 2) {
-      warp_scan_step<2, 4>(m, wl, lane, cx, cy, cz, 2, 0, qx, qy, qz, tau, max_bits, L);  // 125 cells
-    } else if (ring == 3) {
+    if (ring <= 3) {
+      if (!occ_loaded) {
+        const int bx0 = (cx - 3) >> 2, by0 = (cy - 3) >> 2, bz0 = (cz - 3) >> 2;
+        const int nx = ((cx + 3) >> 2) - bx0 + 1, ny = ((cy + 3) >> 2) - by0 + 1, nz = ((cz + 3) >> 2) - bz0 + 1;  // 2 or 3 each
+        if (lane < nx * ny * nz) {
+          obx = bx0 + lane % nx, oby = by0 + (lane / nx) % ny, obz = bz0 + lane / (nx * ny);
+          occ = __ldg(m.occ + occ_word_of(m, obx, oby, obz));
+        }
+        occ_loaded = true;
+      }
+      const int n_list = occ_ring_list(m, wl, lane, occ, obx, oby, obz, cx, cy, cz, ring, qx, qy, qz, tau);
 #pragma unroll 1
-      for (int idx0 = 0; idx0 < 343; idx0 += 128) warp_scan_step<3, 4>(m, wl, lane, cx, cy, cz, 3, idx0, qx, qy, qz, tau, max_bits, L);
+      for (int idx0 = 0; idx0 < n_list; idx0 += 128) warp_scan_step<0, 4, true>(m, wl, lane, cx, cy, cz, n_list, idx0, qx, qy, qz, tau, max_bits, L);
     } else {
       const int side = 2 * ring + 1, total = side * side * side;
 #pragma unroll 1

@@ -50,6 +50,7 @@ __global__ void k_cells_ensure(MapView m, const float4* __restrict__ pts, uint32
         }
         m.table[s].head = b;
         atomicAdd(&m.ctr->n_cells, 1u);
+        atomicOr(&m.occ[occ_word_of(m, cx >> 2, cy >> 2, cz >> 2)], 1ull << occ_bit_of(cx, cy, cz));
         found = s;
         break;
       }
@@ -484,6 +485,10 @@ int map_alloc(lio_ctx* c) {
   LIO_CUDA(cudaMalloc(&m.table, sizeof(HashEntry) * (size_t)c->table_cap));
   LIO_CUDA(cudaMalloc(&m.slots, sizeof(float4) * kSlots * (size_t)m.pool_cap));
   LIO_CUDA(cudaMalloc(&m.next, sizeof(uint32_t) * (size_t)m.pool_cap));
+  // occupancy words: >= one per 2 cells of capacity (a 4x4x4 block usually holds several cells, so most words stay private)
+  const uint64_t occ_words = next_pow2(std::max<uint64_t>(1u << 14, cells / 2));
+  m.occ_mask = (uint32_t)(occ_words - 1);
+  LIO_CUDA(cudaMalloc(&m.occ, sizeof(unsigned long long) * (size_t)occ_words));
   LIO_CUDA(cudaMalloc(&m.ctr, sizeof(MapCounters)));
   LIO_CUDA(cudaMalloc(&c->boxes_dev, sizeof(float) * 6 * 64));
   LIO_CUDA(cudaMemsetAsync(m.ctr, 0, sizeof(MapCounters), c->stream));
@@ -495,6 +500,7 @@ void map_free(lio_ctx* c) {
   cudaFree(m.table);
   cudaFree(m.slots);
   cudaFree(m.next);
+  cudaFree(m.occ);
   cudaFree(m.ctr);
   cudaFree(c->boxes_dev);
   cudaFree(c->batch_pts);
@@ -513,6 +519,7 @@ int map_clear(lio_ctx* c) {
   LIO_CUDA(cudaMemsetAsync(m.table, 0xFF, sizeof(HashEntry) * (size_t)c->table_cap, c->stream));
   LIO_CUDA(cudaMemsetAsync(m.slots, 0xFF, sizeof(float4) * kSlots * (size_t)m.pool_cap, c->stream));
   LIO_CUDA(cudaMemsetAsync(m.next, 0xFF, sizeof(uint32_t) * (size_t)m.pool_cap, c->stream));
+  LIO_CUDA(cudaMemsetAsync(m.occ, 0, sizeof(unsigned long long) * ((size_t)m.occ_mask + 1), c->stream));
   // keep next_id and the sticky error word, zero the rest
   LIO_CUDA(cudaMemsetAsync(&m.ctr->pool_top, 0, sizeof(uint32_t) * 3, c->stream));
   return LIO_OK;

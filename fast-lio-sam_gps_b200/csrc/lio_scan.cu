@@ -195,6 +195,48 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
   }
 }
 
+// 8-lane-group form of the leftover search (four queries per warp): used for generic query batches (lio_map_knn), whose
+// deferred queries are mostly shallow (one ring) - there four queries per warp beat one; the scan path uses the warp form.
+template <bool XFORM, bool DEV>
+__global__ void __launch_bounds__(kKnnBlock) k_knn_left8(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
+                                                        StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
+                                                        float* __restrict__ nn_d2, int* __restrict__ nn_cnt, uint32_t* __restrict__ ctr,
+                                                        uint32_t* __restrict__ ctr_next, uint32_t* __restrict__ stats,
+                                                        const IekfCtl* __restrict__ ctl) {
+  __shared__ StateArg s_st;
+  const Group<8> g;
+  const int groups_per_block = kKnnBlock / 8;
+  const int gid = blockIdx.x * groups_per_block + (threadIdx.x / 8);
+  const int gstride = gridDim.x * groups_per_block;
+  const bool skip = DEV && (ctl->finished || !ctl->converge);  // the tile kernel did not run: ctr is still zero
+  const int n_left = skip ? 0 : (int)ctr[1];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    ctr_next[0] = ctr_next[1] = 0u;  // the next search uses the other counter pair
+    if (stats && !skip) atomicAdd(stats, (uint32_t)n_left);
+  }
+  if (skip) return;
+  const StateArg& st = block_state<DEV>(st_param, ctl, s_st);
+  const float4 pad = make_float4(0.f, 0.f, 0.f, __uint_as_float(kEmptyId));
+  const float inf = __int_as_float(0x7f800000);
+  for (int j = gid; j < n_left; j += gstride) {
+    const uint32_t i = __ldg(left + j);
+    const float4 b = __ldg(pts + i);
+    float qx = b.x, qy = b.y, qz = b.z;
+    if (XFORM) body_to_world(st, b.x, b.y, b.z, qx, qy, qz);
+    unsigned long long key;
+    uint32_t ref;
+    int cnt;
+    knn_search<8>(m, g, qx, qy, qz, max_d2, key, ref, cnt);
+    cnt = min(cnt, k);
+    if (g.gl < k) {
+      const bool have = g.gl < cnt;
+      nn[(size_t)i * k + g.gl] = have ? __ldg(m.slots + ref) : pad;
+      if (nn_d2) nn_d2[(size_t)i * k + g.gl] = have ? __uint_as_float((uint32_t)(key >> 32)) : inf;
+    }
+    if (g.gl == 0) nn_cnt[i] = cnt;
+  }
+}
+
 // Per-query search (lio_knn.cuh, one warp per query: knn_search_warp) of the queries the tile kernel deferred.
 constexpr int kLeftGridMult = 4;  // blocks per SM of k_knn_left
 template <bool XFORM, bool DEV>
@@ -721,6 +763,8 @@ int scan_alloc(lio_ctx* c) {
       LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_hilbert, &hil, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
       LIO_CUDA(cudaStreamSynchronize(c->stream));
     }
+    e = getenv("LIO_BATCH_LEFT");
+    c->batch_left_warp = (e && std::strcmp(e, "warp") == 0) ? 1 : 0;
     e = getenv("LIO_SORT_GRAPH");
     c->sort_graph_ok = !(e && std::strcmp(e, "0") == 0);
     e = getenv("LIO_MAP_GRAPH");
@@ -943,7 +987,11 @@ int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float
     c->tile_flip ^= 1;
     k_knn_tile<false, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, q_dev, c->tile_vals[1], n, st, k, max_d2, out_nn,
                                                                                   out_d2, out_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats);
-    k_knn_left<false, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
+    if (c->batch_left_warp)
+      k_knn_left<false, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
+                                                                         ctr, ctr_next, c->tile_stats, nullptr);
+    else
+      k_knn_left8<false, false><<<c->n_sms * 4, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
                                                                          ctr, ctr_next, c->tile_stats, nullptr);
     c->launches += 1;
   } else {

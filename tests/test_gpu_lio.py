@@ -60,8 +60,11 @@ def test_knn_bit_exact(pair, small_world):
     assert (gc < 3).any() and (gc == 3).any()  # both padded and full rows were exercised
 
 
-def test_knn_ring_expansion_is_exact(pkg, orc):
-    """Sparse map + large radius: the answer lies several hash cells away, so rings 2.. must be searched."""
+@pytest.mark.parametrize("left", ["group", "warp"])
+def test_knn_ring_expansion_is_exact(pkg, orc, left, monkeypatch):
+    """Sparse map + large radius: the answer lies several hash cells away, so rings 2.. must be searched.  Both forms of
+    the leftover kernel: 8-lane groups (generic batches) and warp per query with the occupancy words (the scan path's)."""
+    monkeypatch.setenv("LIO_BATCH_LEFT", left)
     rng = np.random.default_rng(8)
     m = rng.uniform(-20, 20, (3000, 3)).astype(np.float32)
     q = rng.uniform(-22, 22, (4000, 3)).astype(np.float32)
