@@ -79,7 +79,7 @@ struct lio_ctx {
   uint32_t* blk_cnt = nullptr;  // per-block counts for the ordered compaction (2 x blocks)
   float4* list_add = nullptr;
   float4* list_nodown = nullptr;
-  // tile kNN: Morton order of the scan (lio_knn_tile.cuh)
+  // tile kNN: curve order of the scan (lio_knn_tile.cuh)
   uint32_t* tile_keys[2] = {nullptr, nullptr};
   uint32_t* tile_vals[2] = {nullptr, nullptr};
   void* tile_tmp = nullptr;

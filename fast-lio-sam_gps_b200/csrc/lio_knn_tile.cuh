@@ -2,7 +2,7 @@
 // Replaces KD_TREE::Nearest_Search for a whole scan (ikd-Tree, absent submodule) with the same result
 // as lio_knn.cuh's per-query search: the exact k<=5 nearest map points within max_d2, ascending (squared distance, id).
 //
-//   order   : queries are visited in Morton order of their map cell (k_tile_keys + one radix sort per scan), so the 32
+//   order   : queries are visited in space-filling-curve order (Hilbert by default) of their map cell (k_tile_keys + one radix sort per scan), so the 32
 //             queries of a warp usually fall in one or two cells;
 //   stage   : the warp probes every cell of the tile's bounding box grown by E cells (lane-parallel hash probes), then
 //             reads the hit buckets four at a time (one 128-byte line per 8 lanes, float4 per lane) and compacts the
@@ -12,7 +12,7 @@
 //   exact   : a lane is done when its 5th distance (max_d2 if it found fewer) is below its distance to the boundary
 //             of the staged box; otherwise the tile is re-staged with E+1 (E = 1..3) for the lanes still pending;
 //   leftover: queries of incoherent tiles (beyond the first kTileMaxSub sub-tiles) and of sub-tiles whose box or
-//             candidate count overflows the staging area are appended to a list that the per-query 8-lane search of
+//             candidate count overflows the staging area are appended to a list that the per-query search (one warp per query on the scan path) of
 //             lio_knn.cuh (k_knn_left) finishes, spread over the whole GPU.
 #pragma once
 #include "lio_knn.cuh"
@@ -190,7 +190,7 @@ __device__ __forceinline__ int tile_stage(const MapView& m, TileSmem& sm, int la
 
 // Searches one tile.  Per lane: (qx,qy,qz) and `valid`.  On return, lanes whose bit is set in the result mask still
 // need the per-query fallback; every other valid lane has had `emit(L, cnt)` called while its staged points were live.
-// A tile whose queries are spread out (a jump in the Morton order) is served as up to kTileMaxSub sub-tiles: the lanes
+// A tile whose queries are spread out (a jump in the curve order, or a sparse region) is served as up to kTileMaxSub sub-tiles: the lanes
 // within kTileSpan cells of the first pending lane go first; what is left is returned as not served (serialising many
 // one-query sub-tiles in one warp is a chain of dependent memory latencies: the per-query kernel spreads them out).
 template <typename Emit>

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(kKnnBlock) k_knn_batch(MapView m, const float4
 }
 
 // ---------------------------------------------------------------- K3, tile form (lio_knn_tile.cuh)
-// sort keys: Morton code of the query's map cell at the current state
+// sort keys: curve index (tile_key: Hilbert by default) of the query's map cell at the current state
 template <bool XFORM>
 __global__ void __launch_bounds__(256) k_tile_keys(MapView m, const float4* __restrict__ pts, int n, StateArg st, uint32_t* __restrict__ keys,
                                                    uint32_t* __restrict__ vals) {
@@ -867,7 +867,7 @@ int tile_ensure(lio_ctx* c, uint32_t n) {
   return LIO_OK;
 }
 
-// Morton order of n query points (body points at `st` when xform) -> c->tile_vals[1]
+// tile order (sorted curve keys) of n query points (body points at `st` when xform) -> c->tile_vals[1]
 static int tile_order(lio_ctx* c, const float4* pts, int n, const StateArg& st, bool xform) {
   int rc = tile_ensure(c, (uint32_t)n);
   if (rc) return rc;
@@ -1156,7 +1156,7 @@ int iekf_update_device(lio_ctx* c, double* state, double* P_io, double R, int ma
   k_iekf_begin<<<1, 256, 0, c->stream>>>(c->iekf_ctl, c->io_dev);
   c->launches += 1;
   for (int i = -1; i < max_iter; ++i) {
-    int rc = scan_knn(c, state, true);  // by-value state: only the once-per-scan Morton keys use it (the propagated state)
+    int rc = scan_knn(c, state, true);  // by-value state: only the once-per-scan tile keys use it (the propagated state)
     if (rc == LIO_OK) rc = scan_plane_reduce(c, nullptr, false, true, true, i, seq);
     if (rc) return rc;
   }

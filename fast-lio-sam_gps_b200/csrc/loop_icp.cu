@@ -5,7 +5,7 @@
 // = Eigen::umeyama without scaling, DefaultConvergenceCriteria, getFitnessScore) follow SURVEY.md §9.4; operation order is
 // that of oracle/orc_icp.cpp so that transforms, iteration counts and scores compare bit-for-bit.
 //
-// Target side: one implicit balanced tree per target cloud over Morton-sorted points; a leaf is 8 float4 = one 128-byte
+// Target side: one implicit balanced tree per target cloud over its points in Hilbert order; a leaf is 8 float4 = one 128-byte
 // line, a node holds the boxes of its two children (64 bytes).  Search is exact (box pruning with a relative slack, ties
 // -> smaller original index) and unbounded, as pcl's kd-tree search is; max_corr_dist is applied afterwards.
 // Reductions are exact 64-bit fixed-point sums (order independent), so the parallel result equals the serial oracle's.
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kBlock) k_tree_keys(const TreeDev* __restrict_
   vals[i] = l;
 }
 
-// tree_pts[pts_off + r] = (xyz of the r-th point in Morton order, original index); leaves padded with +inf points
+// tree_pts[pts_off + r] = (xyz of the r-th point in curve order, original index); leaves padded with +inf points
 __global__ void __launch_bounds__(kBlock) k_tree_gather(const TreeDev* __restrict__ trees, int n_trees, const uint32_t* __restrict__ cmp_off,
                                                         const uint32_t* __restrict__ pad_off, uint32_t n_pad_total,
                                                         const uint32_t* __restrict__ vals_sorted, const float4* __restrict__ vox,
