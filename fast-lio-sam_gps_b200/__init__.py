@@ -82,6 +82,7 @@ LIO_SYMBOLS = {
     "lio_map_export": (C.c_int, [C.c_void_p, _f32p, _u32p, C.c_int, _i32p]),
     "lio_map_knn": (C.c_int, [C.c_void_p, _f32p, C.c_int, C.c_int, C.c_float, _u32p, _f32p, _f32p, _i32p]),
     "lio_scan_upload": (C.c_int, [C.c_void_p, _f32p, C.c_int]),
+    "lio_scan_prefetch": (C.c_int, [C.c_void_p, _f32p, C.c_int]),
     "lio_scan_set_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "lio_h_share": (C.c_int, [C.c_void_p, _f64p, C.c_int, _f64p, _f64p, _i32p, _f64p]),
     "lio_h_share_rows": (C.c_int, [C.c_void_p, _f64p, C.c_int, _u8p, _f64p, _f64p, _i32p]),
@@ -218,6 +219,10 @@ class LioContext:
         """Upload from a raw (ideally pinned) host pointer to n*3 floats."""
         self.scan_n = n
         self._check(self.lib.lio_scan_upload(self.h, C.cast(host_ptr, _f32p), n))
+
+    def scan_prefetch_ptr(self, host_ptr, n):
+        """Start the H2D copy of the next scan (pinned host pointer) on the copy stream; see lio_scan_prefetch."""
+        self._check(self.lib.lio_scan_prefetch(self.h, C.cast(host_ptr, _f32p), n))
 
     def scan_set_device(self, dev_ptr, n):
         self.scan_n = n

@@ -158,6 +158,12 @@ void lio_ctx_destroy(lio_ctx* c) {
   scan_free(c);
   map_free(c);
   if (c->stage_host) cudaFree(c->stage_host);
+  for (int k = 0; k < 2; ++k) {
+    if (c->pf_dev[k]) cudaFree(c->pf_dev[k]);
+    if (c->pf_copied[k]) cudaEventDestroy(c->pf_copied[k]);
+    if (c->pf_consumed[k]) cudaEventDestroy(c->pf_consumed[k]);
+  }
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -322,7 +328,55 @@ int lio_scan_upload(lio_ctx* c, const float* body_xyz, int n) {
   c->nn_valid = false;
   c->order_valid = false;
   if (n == 0) return LIO_OK;
+  if (c->pf_slot >= 0 && c->pf_ptr == body_xyz && c->pf_n == n) {  // this scan was prefetched: no copy on the main stream
+    const int k = c->pf_slot;
+    c->pf_slot = -1;
+    c->pf_ptr = nullptr;
+    LIO_CUDA(cudaStreamWaitEvent(c->stream, c->pf_copied[k], 0));
+    launch_expand_xyz(c, c->pf_dev[k], n, c->body);
+    LIO_CUDA(cudaEventRecord(c->pf_consumed[k], c->stream));
+    c->pf_used[k] = true;
+    LIO_CUDA(cudaGetLastError());
+    return LIO_OK;
+  }
   return upload_xyz(c, body_xyz, n, c->body);
+}
+
+/* Starts the host->device copy of the NEXT scan on a separate copy stream (double-buffered staging), so it overlaps the
+ * kernels of the scan being processed; lio_scan_upload with the same pointer and count then only waits for that copy.
+ * The host buffer must stay unchanged (and, to overlap at all, pinned) until that lio_scan_upload. */
+int lio_scan_prefetch(lio_ctx* c, const float* body_xyz, int n) {
+  int rc = check_ctx(c);
+  if (rc) return rc;
+  if (n <= 0 || (uint32_t)n > c->cfg.max_scan || !body_xyz) {
+    set_error("lio_scan_prefetch: %d points (max_scan %u) or null pointer", n, c->cfg.max_scan);
+    return LIO_E_ARG;
+  }
+  if (!c->copy_stream) {
+    LIO_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; ++k) {
+      LIO_CUDA(cudaEventCreateWithFlags(&c->pf_copied[k], cudaEventDisableTiming));
+      LIO_CUDA(cudaEventCreateWithFlags(&c->pf_consumed[k], cudaEventDisableTiming));
+    }
+  }
+  const int k = c->pf_next;
+  const size_t bytes = sizeof(float) * 3 * (size_t)n;
+  if (bytes > c->pf_cap[k]) {
+    if (c->pf_dev[k]) cudaFree(c->pf_dev[k]);  // synchronises: nothing still reads the old buffer
+    c->pf_dev[k] = nullptr;
+    c->pf_cap[k] = 0;
+    c->pf_used[k] = false;
+    LIO_CUDA(cudaMalloc(&c->pf_dev[k], sizeof(float) * 3 * (size_t)c->cfg.max_scan));
+    c->pf_cap[k] = sizeof(float) * 3 * (size_t)c->cfg.max_scan;
+  }
+  if (c->pf_used[k]) LIO_CUDA(cudaStreamWaitEvent(c->copy_stream, c->pf_consumed[k], 0));  // the slot's last reader is done
+  LIO_CUDA(cudaMemcpyAsync(c->pf_dev[k], body_xyz, bytes, cudaMemcpyHostToDevice, c->copy_stream));
+  LIO_CUDA(cudaEventRecord(c->pf_copied[k], c->copy_stream));
+  c->pf_slot = k;
+  c->pf_ptr = body_xyz;
+  c->pf_n = n;
+  c->pf_next = k ^ 1;
+  return LIO_OK;
 }
 
 int lio_scan_set_device(lio_ctx* c, const void* body_xyzw_dev, int n) {

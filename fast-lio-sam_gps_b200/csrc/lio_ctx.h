@@ -117,6 +117,15 @@ struct lio_ctx {
   // pinned staging for uploads
   float* stage_host = nullptr;
   size_t stage_bytes = 0;
+  // lio_scan_prefetch: the next scan's H2D copy on its own stream, double-buffered, consumed by lio_scan_upload
+  cudaStream_t copy_stream = nullptr;
+  float* pf_dev[2] = {nullptr, nullptr};
+  size_t pf_cap[2] = {0, 0};
+  cudaEvent_t pf_copied[2] = {nullptr, nullptr};    // H2D of the slot finished (copy stream)
+  cudaEvent_t pf_consumed[2] = {nullptr, nullptr};  // the slot was expanded into body (main stream)
+  bool pf_used[2] = {false, false};
+  int pf_next = 0, pf_slot = -1, pf_n = 0;
+  const float* pf_ptr = nullptr;
 
   // fov_segment state
   bool lm_init = false;

@@ -76,6 +76,11 @@ int lio_map_knn(lio_ctx* ctx, const float* q_xyz, int n, int k, float max_sqdist
 /* ---- scan + measurement model: replaces h_share_model -------------------------------------------- */
 /* feats_down_body: n points (xyz, stride 3 floats, HOST memory) -> device. Invalidates cached neighbours. */
 int lio_scan_upload(lio_ctx* ctx, const float* body_xyz, int n);
+/* Optional: start the host->device copy of the NEXT scan on a separate copy stream so that it overlaps the kernels of the
+ * scan in flight (the LiDAR driver hands over scan i+1 while scan i is in the filter).  A following lio_scan_upload with
+ * the same pointer and count consumes the prefetched copy; any other upload ignores it.  The buffer must stay unchanged
+ * until then, and should be pinned. */
+int lio_scan_prefetch(lio_ctx* ctx, const float* body_xyz, int n);
 /* Same, from a DEVICE pointer to n float4 (x,y,z,unused). */
 int lio_scan_set_device(lio_ctx* ctx, const void* body_xyzw_dev, int n);
 

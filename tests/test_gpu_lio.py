@@ -60,6 +60,32 @@ def test_knn_bit_exact(pair, small_world):
     assert (gc < 3).any() and (gc == 3).any()  # both padded and full rows were exercised
 
 
+def test_scan_prefetch_equals_plain_upload(pair, small_world):
+    """lio_scan_prefetch + lio_scan_upload (copy on the copy stream, double-buffered) feeds the filter the same scan as a
+    plain lio_scan_upload; an upload from another pointer ignores a pending prefetch."""
+    g, _ = pair
+    st = small_world["start"]
+    a = np.ascontiguousarray(small_world["scan"], np.float32)
+    b = np.ascontiguousarray(a[::-1] + np.float32(0.01))
+    ref = {}
+    for name, s in (("a", a), ("b", b)):
+        g.scan_upload(s)
+        ref[name] = g.h_share(st, True)
+    for rnd in range(3):  # alternate slots: a, b, a through the prefetch path
+        name, s = (("a", a), ("b", b))[rnd % 2]
+        g.scan_prefetch_ptr(s.ctypes.data, len(s))
+        g.scan_upload_ptr(s.ctypes.data, len(s))
+        H, z, n_eff, res = g.h_share(st, True)
+        assert n_eff == ref[name][2] and np.array_equal(H, ref[name][0]) and np.array_equal(z, ref[name][1])
+    g.scan_prefetch_ptr(b.ctypes.data, len(b))  # pending prefetch of b, but a is what gets uploaded
+    g.scan_upload_ptr(a.ctypes.data, len(a))
+    H, z, n_eff, res = g.h_share(st, True)
+    assert n_eff == ref["a"][2] and np.array_equal(H, ref["a"][0])
+    g.scan_upload_ptr(b.ctypes.data, len(b))  # the stale prefetch of b is still valid for b's pointer and is consumed here
+    H, z, n_eff, res = g.h_share(st, True)
+    assert n_eff == ref["b"][2] and np.array_equal(H, ref["b"][0])
+
+
 @pytest.mark.parametrize("left", ["group", "warp"])
 def test_knn_ring_expansion_is_exact(pkg, orc, left, monkeypatch):
     """Sparse map + large radius: the answer lies several hash cells away, so rings 2.. must be searched.  Both forms of
