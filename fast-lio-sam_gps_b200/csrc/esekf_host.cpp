@@ -85,7 +85,6 @@ int iekf_update_host(lio_ctx* c, double* state, double* P_io, double R, int max_
       for (int k = 0; k < kDof; ++k) s += (K_x[r * kDof + k] - (r == k ? 1.0 : 0.0)) * dx_new[k];
       dxu[r] = s;
     }
-    const State x_before = x;
     state_boxplus(x, dxu);
     if (iter_states) store(x, iter_states + LIO_STATE_DOUBLES * done);
     ++done;
@@ -110,7 +109,9 @@ int iekf_update_host(lio_ctx* c, double* state, double* P_io, double R, int max_
       }
       {
         double J[4];
-        s2_jacobian(x.grav, x_before.grav, dxu + 21, J);
+        // [RECALL, unverified against the absent esekfom.hpp] upstream evaluates Mx at x_propagated here as well as at the top
+        // of the loop (its `x_before` copy is never read); the oracle and the device loop make the same choice
+        s2_jacobian(x.grav, x_prop.grav, dxu + 21, J);
         left_block(L, kDof, 21, 2, J);
         left_block(K_x, kDof, 21, 2, J);
         right_block(L, kDof, kDof, 21, 2, J);

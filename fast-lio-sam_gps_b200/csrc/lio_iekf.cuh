@@ -250,7 +250,7 @@ __device__ __noinline__ void iekf_step_block(IekfCtl* ctl, IekfIO* io, const dou
   __syncthreads();
   if (tid == 0) {
     State x = load(ctl->x);
-    const State x_before = x;
+    const State x_prop = load(ctl->x_prop);
     double dxu[kDof];
     for (int k = 0; k < kDof; ++k) dxu[k] = sm.dxu[k];
     state_boxplus(x, dxu);
@@ -276,7 +276,7 @@ __device__ __noinline__ void iekf_step_block(IekfCtl* ctl, IekfIO* io, const dou
         for (int k = 0; k < 9; ++k) sm.J[b][k] = J.m[k];
       }
       double J2[4];
-      s2_jacobian(x.grav, x_before.grav, dxu + 21, J2);
+      s2_jacobian(x.grav, x_prop.grav, dxu + 21, J2);  // Mx at x_propagated, as esekf_host.cpp
       for (int k = 0; k < 4; ++k) sm.J[2][k] = J2[k];
     }
   }

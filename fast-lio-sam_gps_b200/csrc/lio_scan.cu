@@ -354,8 +354,13 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
       float4 pl = make_float4(0.f, 0.f, 0.f, 0.f);
       float pabcd[4];
       bool fit_ok = false;
+      // point_selected_surf[i] persists between the calls of one scan: the search re-derives it
+      // (five neighbours, the fifth within max_sqdist); a call that reuses the cached neighbours only looks at the
+      // points the previous call left selected, so a point rejected by esti_plane or by the weight test stays out
+      // until the next search.
+      const bool cand = refit ? (nn_cnt[i] >= kK) : (sel[i] != 0);
       if (refit) {
-        if (nn_cnt[i] >= kK) {
+        if (cand) {
           float P[kK][3];
 #pragma unroll
           for (int k = 0; k < kK; ++k) {
@@ -367,7 +372,7 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
           fit_ok = esti_plane(pabcd, P, 0.1f);
         }
         pfit[i] = fit_ok ? make_float4(pabcd[0], pabcd[1], pabcd[2], pabcd[3]) : make_float4(__int_as_float(0x7fc00000), 0.f, 0.f, 0.f);
-      } else {
+      } else if (cand) {
         const float4 f = pfit[i];
         fit_ok = f.x == f.x;  // NaN marks "no valid plane"
         pabcd[0] = f.x, pabcd[1] = f.y, pabcd[2] = f.z, pabcd[3] = f.w;

@@ -205,11 +205,16 @@ int h_share_model(Ctx& c, const St& s, bool converge, double* HTH, double* HTz, 
         d[0] = hits[k].x; d[1] = hits[k].y; d[2] = hits[k].z;
         std::memcpy(&d[3], &hits[k].id, 4);
       }
-      // reference: selected = (points_near.size() >= 5) && (sqdist[4] <= 5) with an unbounded
-      // search; searching with max_d2 = 5 gives the identical flag.
+      // reference: point_selected_surf[i] = (points_near.size() >= 5) && (sqdist[4] <= 5) with an
+      // unbounded search; searching with max_d2 = 5 gives the identical flag.
+      sc.sel[i] = cnt >= kK ? 1 : 0;
     }
+    // point_selected_surf[i] is a file-scope flag upstream: it is re-derived from the
+    // search only when ekfom_data.converge is set; on the calls that reuse the cached neighbours a point
+    // that failed esti_plane or the weight test in the PREVIOUS call stays out ("if (!selected) continue"),
+    // so the selected set can only shrink between two searches.
+    if (!sc.sel[i]) continue;
     sc.sel[i] = 0;
-    if (sc.nn_cnt[i] < kK) continue;
     float P[kK][3];
     for (int k = 0; k < kK; ++k) {
       const float* d = &sc.nn[(size_t(i) * kK + k) * 4];
@@ -384,7 +389,6 @@ int iekf_update(Ctx& c, St& x, M23& P, double R, int max_iter, const double* lim
       for (int k = 0; k < 23; ++k) s += (K_x(r, k) - (r == k ? 1.0 : 0.0)) * dx_new.a[k];
       dx_.a[r] = s;
     }
-    St x_before = x;
     boxplus(x, dx_);
     if (iter_states) pack(x, iter_states + 36 * done);
     ++done;
@@ -409,7 +413,8 @@ int iekf_update(Ctx& c, St& x, M23& P, double R, int max_iter, const double* lim
       }
       {
         Mat<2, 1> seg; seg.a[0] = dx_.a[21]; seg.a[1] = dx_.a[22];
-        Mat<2, 2> J = S2_Nx_yy(x.grav) * S2_Mx(x_before.grav, seg);
+        // [RECALL, unverified: esekfom.hpp is absent] upstream calls x_propagated.S2_Mx(...) here too; its x_before is unused
+        Mat<2, 2> J = S2_Nx_yy(x.grav) * S2_Mx(x_prop.grav, seg);
         project_rows<2>(L, 21, J);
         for (int cc = 0; cc < 12; ++cc) {
           double tt[2];

@@ -63,3 +63,19 @@ def small_world(synth):
     scan = synth.make_scan(scene, R, t, kind="vlp16")
     truth = synth.make_state(R, t)
     return dict(scene=scene, map=map_pts, scan=scan, truth=truth, start=synth.perturb_state(truth))
+
+
+@pytest.fixture(scope="session")
+def planted(synth):
+    """Ground-plane map and a scan of it seen from 1.2 m; at `off` the sensor is 15 cm too high, so the weight test
+    s = 1 - 0.9|pd2|/sqrt(range) > 0.9 fails for the points with sqrt(range) < 1.35 and passes for the far ones."""
+    g = np.arange(-12, 12, 0.5, dtype=np.float32) + 0.25
+    gx, gy = np.meshgrid(g, g)
+    m = np.stack([gx.ravel(), gy.ravel(), np.full(gx.size, 5.0, np.float32)], 1)  # (esti_plane cannot express a plane through the origin)
+    rng = np.random.default_rng(7)
+    xy = rng.uniform(-8, 8, (3000, 2)).astype(np.float32)
+    scan = np.concatenate([xy, np.full((len(xy), 1), -1.2, np.float32)], 1)  # body frame = world shifted by the height
+    truth = synth.make_state(np.eye(3), np.array([0.0, 0.0, 6.2]))
+    off = synth.make_state(np.eye(3), np.array([0.0, 0.0, 6.35]))
+    return m, scan, truth, off
+

@@ -131,10 +131,14 @@ def test_h_share_parity(pkg, orc, small_world, ext):
     st = w["start"].copy()
     if ext:
         st[21:24] = [0.05, -0.02, 0.1]
-    for redo, state in ((True, st), (False, w["truth"] if not ext else st), (True, w["truth"])):
+    prev_sel = None
+    for redo, state in ((True, st), (False, w["truth"] if not ext else st), (False, st), (True, w["truth"])):
         gH, gz, gn, gr = g.h_share(state, redo)
         oH, oz, on, orr = o.h_share(state, redo)
         go, oo = g.scan_get(), o.scan_get()
+        if not redo:  # point_selected_surf persists between searches: the set can only shrink
+            assert (go["sel"] <= prev_sel).all()
+        prev_sel = go["sel"].copy()
         assert np.array_equal(go["world"], oo["world"])
         assert np.array_equal(go["nn_cnt"], oo["nn_cnt"])
         assert np.array_equal(go["nn_ids"], oo["nn_ids"])  # kNN index sets: bit-exact
@@ -147,6 +151,34 @@ def test_h_share_parity(pkg, orc, small_world, ext):
         assert rel_err(gH, oH) < 1e-11  # same f64 rows, only the summation order differs
         assert abs(gr - orr) <= 1e-9 * orr
         assert np.array_equal(gH, gH.T)
+    g.close()
+
+
+def test_point_selected_surf_persists_gpu(pkg, orc, planted):
+    """A point that fails the weight test in call 1 stays unselected in the calls that reuse the cached neighbours, although
+    it would pass at the new state (the oracle-side statement: test_oracle_lio.py::test_point_selected_surf_persists...)."""
+    m, scan, truth, off = planted
+    g = pkg.LioContext(0.5, max_points=1 << 16, max_scan=1 << 12)
+    o = orc.OracleLio(0.5, nthreads=0)
+    g.map_build(m)
+    o.map_build(m)
+    g.scan_upload(scan)
+    o.scan_upload(scan)
+    near = np.sqrt(np.linalg.norm(scan, axis=1)) < 1.33
+    sels = []
+    for redo, state in ((True, off), (False, truth), (True, truth), (False, off), (False, truth)):
+        gH, gz, gn, _ = g.h_share(state, redo)
+        oH, oz, on, _ = o.h_share(state, redo)
+        go, oo = g.scan_get(), o.scan_get()
+        assert np.array_equal(go["sel"], oo["sel"]) and gn == on == go["sel"].sum()
+        assert rel_err(gH, oH) < 1e-11 and rel_err(gz, oz) < 1e-9
+        sels.append(go["sel"].copy())
+    assert sels[0][near].sum() == 0 and sels[1][near].sum() == 0 and np.array_equal(sels[0], sels[1])
+    assert sels[2].all()
+    assert sels[3][near].sum() == 0 and np.array_equal(sels[3], sels[4])
+    # the rows entry point and the device-resident loop go through the same kernel: same flag
+    sel_r, rows, z, n_r = g.h_share_rows(truth, False)
+    assert np.array_equal(sel_r, sels[4]) and n_r == sels[4].sum()
     g.close()
 
 
