@@ -42,6 +42,14 @@ int main() {
     }
     RegistrationOutput r = lc.performLoopClosure(kfs[2], kfs, 0);
     std::printf("adapters: loop closure converged=%d valid=%d score=%g\n", (int)r.is_converged_, (int)r.is_valid_, r.score_);
+    if (!r.is_valid_ || !r.is_converged_) throw std::runtime_error("identical clouds 10 cm apart must verify");
+    // loop_closure.cpp:85-90: both flags are set only inside the gate; a pair that converges but scores above the threshold
+    // comes back with is_valid_ == is_converged_ == false and score_ still written (loop_closure.h:33-35 defaults otherwise)
+    cfg.icp_score_threshold_ = 0.0;
+    LoopClosureB200 strict(cfg);
+    RegistrationOutput r2 = strict.performLoopClosure(kfs[2], kfs, 0);
+    std::printf("adapters: gated out: converged=%d valid=%d score=%g\n", (int)r2.is_converged_, (int)r2.is_valid_, r2.score_);
+    if (r2.is_valid_ || r2.is_converged_ || !(r2.score_ < 1e300)) throw std::runtime_error("RegistrationOutput flags differ from loop_closure.cpp:85-90");
   } catch (const std::exception &e) {
     std::printf("adapters: FAILED: %s\n", e.what());
     return 1;

@@ -60,10 +60,10 @@ class LoopClosureB200 {
   }
   RegistrationOutput to_output(const loop_result &r) const {  // loop_closure.cpp:83-90
     RegistrationOutput out;
-    out.score_ = r.score;
-    out.is_converged_ = r.converged != 0;
-    if (r.valid) {
-      out.is_valid_ = true;
+    out.score_ = r.score;  // always written (:83)
+    if (r.valid) {         // hasConverged() && score < icp_score_threshold_: the reference sets BOTH flags only here (:85-90),
+      out.is_valid_ = true;  // is_converged_ stays at its default false otherwise (loop_closure.h:33-34)
+      out.is_converged_ = true;
       for (int i = 0; i < 4; ++i)
         for (int j = 0; j < 4; ++j) out.pose_between_eig_(i, j) = (double)r.T[4 * i + j];
     }
