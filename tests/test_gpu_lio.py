@@ -496,8 +496,9 @@ def test_edge_cases_and_errors(pkg, synth, small_world):
 
 
 def test_full_size_properties(pkg, synth):
-    """BASELINE config-2 sizes (131,072-point scan, 2M-point map): size-independent properties instead of the oracle:
-    kNN on a sample vs brute force, H^T H symmetric PSD and equal to the row products, determinism, idempotence."""
+    """BASELINE config-2 sizes (131,072-point scan, 2M-point map): size-independent properties (the oracle comparison at
+    this size is test_parity_at_baseline_config): kNN on a sample vs brute force, H^T H symmetric PSD and equal to the row
+    products, determinism, idempotence."""
     rng = np.random.default_rng(11)
     M, N = 2_000_000, 131_072
     # planar-ish synthetic map: ground + two walls, one point per 0.5 m cell, jittered
@@ -547,3 +548,23 @@ def test_full_size_properties(pkg, synth):
     a, b = g.map_incremental(st, True)
     assert g.map_size() - s1 <= b  # only no-downsample points may accumulate
     g.close()
+
+
+def test_parity_at_baseline_config(pkg, orc, synth):
+    """BASELINE configs[1] at full size (131,072-point OS1-128-shaped scan, 2M-point map), GPU vs the oracle: kNN index
+    sets and plane masks bit-exact after a search and after a cached-neighbour call, H^T H / H^T z to 1e-5, n_eff and the state
+    of every iteration (1e-6), and the live map after map_incremental as a set.  Same function bench.py puts in its line."""
+    import bench
+
+    w = bench.make_iekf_workload(synth, bench.N_SCAN, bench.N_MAP, 2)
+    g = pkg.LioContext(0.5, max_points=bench.N_MAP + 8 * bench.N_SCAN, max_scan=bench.N_SCAN, max_cells=bench.N_MAP // 2)
+    o = orc.OracleLio(0.5, nthreads=0)
+    g.map_build(w["map"])
+    o.map_build(w["map"])
+    P0 = synth.default_cov()
+    for j in range(2):  # the second scan runs against the map the first one grew
+        par = bench.parity_at_config(g, o, w["scans"][j], w["starts"][j], w["truths"][j], P0)
+        assert par["all"], par
+        assert par["n_eff_first_call"] > 0.5 * bench.N_SCAN and par["live_map_points"] > bench.N_MAP
+    g.close()
+    o.close()
