@@ -101,6 +101,7 @@ LIO_SYMBOLS = {
     "lio_timing_reset": (C.c_int, [C.c_void_p]),
     "lio_knn_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "lio_knn_stats_detail": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "lio_tile_profile": (C.c_int, [C.c_void_p, _u32p, C.c_int, _i32p]),
     "lio_gather_probe": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "lio_launch_count": (C.c_int64, [C.c_void_p]),
 }
@@ -332,6 +333,14 @@ class LioContext:
         v = (C.c_uint64 * 4)()
         self._check(self.lib.lio_knn_stats_detail(self.h, v))
         return dict(per_query=int(v[0]), overflow=int(v[1]), incoherent=int(v[2]))
+
+    def tile_profile(self):
+        """(tiles, 4) uint32 per-tile counters of the last scan search (needs LIO_TILE_PROF=1 at context creation)."""
+        n = C.c_int(0)
+        self._check(self.lib.lio_tile_profile(self.h, None, 0, C.byref(n)))
+        out = np.zeros((max(n.value, 1), 4), np.uint32)
+        self._check(self.lib.lio_tile_profile(self.h, _p(out, _u32p), n.value, C.byref(n)))
+        return out[: n.value]
 
     def gather_probe(self, table_bytes=320 << 20, reps=5):
         a, b = C.c_double(0), C.c_double(0)

@@ -723,6 +723,23 @@ int lio_knn_stats_detail(lio_ctx* c, uint64_t* out4) {
   return LIO_OK;
 }
 
+int lio_tile_profile(lio_ctx* c, uint32_t* out4, int cap_tiles, int* n_tiles) {
+  int rc = check_ctx(c);
+  if (rc) return rc;
+  if (!c->tile_prof) {
+    set_error("lio_tile_profile: create the context with LIO_TILE_PROF=1");
+    return LIO_E_STATE;
+  }
+  const int tiles = (c->scan_n + 31) / 32;
+  if (n_tiles) *n_tiles = tiles;
+  const int m = std::min(tiles, cap_tiles);
+  if (out4 && m > 0) {
+    LIO_CUDA(cudaMemcpyAsync(out4, c->tile_prof, sizeof(uint4) * (size_t)m, cudaMemcpyDeviceToHost, c->stream));
+    LIO_CUDA(cudaStreamSynchronize(c->stream));
+  }
+  return LIO_OK;
+}
+
 int64_t lio_launch_count(lio_ctx* c) { return c ? c->launches : 0; }
 
 }  // extern "C"

@@ -82,8 +82,7 @@ struct lio_ctx {
   // tile kNN: curve order of the scan (lio_knn_tile.cuh)
   uint32_t* tile_keys[2] = {nullptr, nullptr};
   uint32_t* tile_vals[2] = {nullptr, nullptr};
-  void* tile_tmp = nullptr;
-  size_t tile_tmp_bytes = 0;
+  void* sort_scratch = nullptr;  // SortScratch (lio_scan.cu): coarse-bin histogram / offsets / cursors of the scan ordering
   uint32_t tile_cap = 0;
   bool order_valid = false;      // tile_vals[1] holds the order of the current scan
   std::vector<std::pair<int, void*>> sort_graphs;  // (padded size, cudaGraphExec_t) of the captured keys + sort passes
@@ -95,6 +94,7 @@ struct lio_ctx {
   int map_graph_launches = 0;    // kernels inside one map_incremental graph
   void* map_args_host = nullptr;
   void* map_args_dev = nullptr;
+  uint4* tile_prof = nullptr;      // LIO_TILE_PROF=1: per-tile {cycles, passes | deferred<<8 | overflow<<16, staged points, cells probed}
   uint32_t* tile_stats = nullptr;  // [0] queries that went to the per-query fallback (debug/bench counter)
   int tile_flip = 0;             // which counter pair the next search uses
   int knn_mode = 1;              // 1 tile (default), 0 per-query groups (LIO_KNN_MODE=group)

@@ -193,9 +193,12 @@ __device__ __forceinline__ int tile_stage(const MapView& m, TileSmem& sm, int la
 // A tile whose queries are spread out (a jump in the curve order, or a sparse region) is served as up to kTileMaxSub sub-tiles: the lanes
 // within kTileSpan cells of the first pending lane go first; what is left is returned as not served (serialising many
 // one-query sub-tiles in one warp is a chain of dependent memory latencies: the per-query kernel spreads them out).
+struct TileProf {  // warp-uniform counters of one tile (debug / profiling hook: lio_tile_profile)
+  int passes, staged, cells;
+};
 template <typename Emit>
 __device__ __forceinline__ unsigned tile_search(const MapView& m, TileSmem& sm, int lane, float qx, float qy, float qz, bool valid,
-                                                float max_d2, Emit&& emit, unsigned* overflow_mask = nullptr) {
+                                                float max_d2, Emit&& emit, unsigned* overflow_mask = nullptr, TileProf* prof = nullptr) {
   const float h = m.cell_size;
   const int cx = vox_of(qx, m.ds) >> m.cell_shift, cy = vox_of(qy, m.ds) >> m.cell_shift, cz = vox_of(qz, m.ds) >> m.cell_shift;
   const int big = 0x3fffffff;
@@ -217,6 +220,11 @@ __device__ __forceinline__ unsigned tile_search(const MapView& m, TileSmem& sm, 
       const int dx = hix - lox + 1, dy = hiy - loy + 1, dz = hiz - loz + 1;
       int n_st = -1;
       if (E <= c_tile_max_e && dx * dy * dz <= kTileMaxCells) n_st = tile_stage(m, sm, lane, lox, loy, loz, dx, dy, dz);
+      if (prof) {
+        prof->passes += 1;
+        prof->staged += max(n_st, 0);
+        prof->cells += dx * dy * dz;
+      }
       if (n_st < 0) {  // too many cells / candidates: these queries take the per-query path
         failed |= sub;
         break;

@@ -7,7 +7,6 @@
 #include <cstdlib>
 #include <cstring>
 #include "lio_ctx.h"
-#include <cub/device/device_radix_sort.cuh>
 #include "lio_knn.cuh"
 #include "lio_knn_tile.cuh"
 #include "lio_plane.cuh"
@@ -84,42 +83,180 @@ __global__ void __launch_bounds__(kKnnBlock) k_knn_batch(MapView m, const float4
 }
 
 // ---------------------------------------------------------------- K3, tile form (lio_knn_tile.cuh)
-// sort keys: curve index (tile_key: Hilbert by default) of the query's map cell at the current state
-template <bool XFORM>
-__global__ void __launch_bounds__(256) k_tile_keys(MapView m, const float4* __restrict__ pts, int n, StateArg st, uint32_t* __restrict__ keys,
-                                                   uint32_t* __restrict__ vals) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const float4 b = __ldg(pts + i);
-    float qx = b.x, qy = b.y, qz = b.z;
-    if (XFORM) body_to_world(st, b.x, b.y, b.z, qx, qy, qz);
-    keys[i] = tile_key(m, qx, qy, qz);
-    vals[i] = (uint32_t)i;
-  }
-}
-
-// Graph form of k_tile_keys: (state, n) come from a small device block refreshed by a memcpy node, so one captured graph
-// (keys + the library's radix-sort passes) serves every scan of up to n_pad points; rows n..n_pad-1 carry the maximal key.
+// Scan ordering: the queries are put in curve order (tile_key: 24-bit Hilbert index of the query's map cell) by a two-level
+// counting sort written for this size (131 k keys that fall in a few thousand distinct cells) - three short, fully parallel
+// kernels instead of the library's radix passes (round 1: cub::DeviceRadixSort, 56 us per scan = 14 % of the step; its
+// chained-scan passes run on 17 blocks at this size):
+//   k_sort_count   key per query; level-1 histogram over the TOP 12 key bits (a 16-cell cube), level-2 histogram over the LOW
+//                  12 bits inside the cube's slot (slots are handed to cubes on first touch); warp-aggregated atomics;
+//   k_sort_scan    block 0: exclusive scan of the 4096 level-1 bins -> start[]; block 1+s: exclusive scan of slot s;
+//   k_sort_place   order[start[cube] + offset[slot][low]++] = query (the same warp aggregation);
+//   k_sort_clear   re-zeroes what this sort touched (off the critical path of the search that follows? no: 2 us, kept simple).
+// The order inside one cell is whatever the atomics produce: it only decides which queries share a warp, every result is
+// written to the query's own row, so nothing downstream depends on it.
 struct KeysArgs {
   double s[36];
   int n;
   int pad;
 };
-__global__ void __launch_bounds__(256) k_tile_keys_g(MapView m, const float4* __restrict__ pts, const KeysArgs* __restrict__ a, int n_pad,
-                                                     uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+constexpr int kSortBins = 4096;  // 12 bits per level
+constexpr uint32_t kSortLowMask = kSortBins - 1;
+constexpr uint32_t kSlotPending = 0xFFFFFFFFu;
+struct SortScratch {
+  uint32_t hist1[kSortBins];      // level 1: queries per cube
+  uint32_t start[kSortBins + 1];  // exclusive scan of hist1
+  uint32_t slot_of[kSortBins];    // cube -> slot + 1 (0: none yet)
+  uint32_t n_slots;
+  uint32_t pad[2];  // [0]: ticket of k_sort_clear; sized so that the counters behind the header are 16-byte aligned
+  // followed by hist2[kSortBins][kSortBins] (slot-major), allocated behind this header
+};
+static_assert(sizeof(SortScratch) % 16 == 0, "level-2 counters must start 16-byte aligned (k_sort_clear stores uint4)");
+__device__ __forceinline__ uint32_t* sort_hist2(SortScratch* sc) { return reinterpret_cast<uint32_t*>(sc + 1); }
+
+// a != nullptr: graph form, (state, n) come from a small device block refreshed by a memcpy node, so one captured graph
+// serves every scan of up to n_grid points.
+template <bool XFORM>
+__global__ void __launch_bounds__(256) k_sort_count(MapView m, const float4* __restrict__ pts, const KeysArgs* __restrict__ a, StateArg st_val, int n_val,
+                                                    uint32_t* __restrict__ keys, SortScratch* __restrict__ sc) {
   __shared__ StateArg s_st;
-  if (threadIdx.x < 36) s_st.s[threadIdx.x] = a->s[threadIdx.x];
+  if (XFORM && threadIdx.x < 36) s_st.s[threadIdx.x] = a ? a->s[threadIdx.x] : st_val.s[threadIdx.x];
   __syncthreads();
-  const int n = a->n;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pad; i += gridDim.x * blockDim.x) {
-    uint32_t key = (1u << kTileKeyBits) - 1u;
-    if (i < n) {
-      const float4 b = __ldg(pts + i);
-      float qx, qy, qz;
-      body_to_world(s_st, b.x, b.y, b.z, qx, qy, qz);
-      key = tile_key(m, qx, qy, qz);
-    }
+  const int n = a ? a->n : n_val;
+  const int lane = threadIdx.x & 31;
+  uint32_t* hist2 = sort_hist2(sc);
+  for (int i0 = (blockIdx.x * blockDim.x + threadIdx.x) - lane; i0 < n; i0 += gridDim.x * blockDim.x) {
+    const int i = i0 + lane;
+    const unsigned act = __ballot_sync(0xFFFFFFFFu, i < n);
+    if (i >= n) continue;
+    const float4 b = __ldg(pts + i);
+    float qx = b.x, qy = b.y, qz = b.z;
+    if (XFORM) body_to_world(s_st, b.x, b.y, b.z, qx, qy, qz);
+    const uint32_t key = tile_key(m, qx, qy, qz);
     keys[i] = key;
-    vals[i] = (uint32_t)i;
+    const uint32_t cube = key >> 12;
+    // one atomic per distinct cube / cell of the warp (consecutive raw points mostly share their cell)
+    const unsigned pc = __match_any_sync(act, cube);
+    const int lc = __ffs(pc) - 1;
+    uint32_t slot = 0;
+    if (lane == lc) {
+      atomicAdd(&sc->hist1[cube], (uint32_t)__popc(pc));
+      slot = *reinterpret_cast<volatile uint32_t*>(&sc->slot_of[cube]);
+      if (slot == 0) {
+        const uint32_t old = atomicCAS(&sc->slot_of[cube], 0u, kSlotPending);
+        if (old == 0) {
+          slot = atomicAdd(&sc->n_slots, 1u) + 1u;
+          atomicExch(&sc->slot_of[cube], slot);
+        } else {
+          slot = old;
+        }
+      }
+      while (slot == kSlotPending) slot = *reinterpret_cast<volatile uint32_t*>(&sc->slot_of[cube]);  // another warp is assigning it
+    }
+    slot = __shfl_sync(pc, slot, lc);
+    const unsigned pk = __match_any_sync(act, key);
+    if (lane == __ffs(pk) - 1) atomicAdd(&hist2[(size_t)(slot - 1) * kSortBins + (key & kSortLowMask)], (uint32_t)__popc(pk));
+  }
+}
+
+// exclusive scan of 4096 counters by one block of 512 threads (8 consecutive counters per thread)
+constexpr int kSortScanBlock = 512;
+__device__ __forceinline__ uint32_t block_scan_4096(uint32_t* __restrict__ cnt, uint32_t* s_scan) {
+  constexpr int PER = kSortBins / kSortScanBlock;
+  uint32_t v[PER], sum = 0;
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    v[j] = cnt[threadIdx.x * PER + j];  // (generic pointer: global counters of an earlier launch, or the level-1 copy in shared memory)
+    sum += v[j];
+  }
+  // warp scan, then scan of the 16 warp totals
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t inc = sum;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, off);
+    if (lane >= off) inc += t;
+  }
+  if (lane == 31) s_scan[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < kSortScanBlock / 32 ? s_scan[lane] : 0u;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, w, off);
+      if (lane >= off) w += t;
+    }
+    s_scan[lane] = w;  // inclusive warp totals
+  }
+  __syncthreads();
+  uint32_t run = (warp ? s_scan[warp - 1] : 0u) + inc - sum;
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    cnt[threadIdx.x * PER + j] = run;
+    run += v[j];
+  }
+  return s_scan[kSortScanBlock / 32 - 1];  // total
+}
+
+__global__ void __launch_bounds__(kSortScanBlock) k_sort_scan(SortScratch* __restrict__ sc) {
+  __shared__ uint32_t s_scan[32];
+  if (blockIdx.x == 0) {  // level 1 -> start[] (hist1 itself is left zeroed for the next sort)
+    __shared__ uint32_t s_tmp[kSortBins];
+    for (int e = threadIdx.x; e < kSortBins; e += kSortScanBlock) s_tmp[e] = __ldcg(&sc->hist1[e]);
+    __syncthreads();
+    const uint32_t total = block_scan_4096(s_tmp, s_scan);
+    __syncthreads();
+    for (int e = threadIdx.x; e < kSortBins; e += kSortScanBlock) {
+      sc->start[e] = s_tmp[e];
+      sc->hist1[e] = 0;
+    }
+    if (threadIdx.x == 0) sc->start[kSortBins] = total;
+    return;
+  }
+  const uint32_t n_slots = sc->n_slots;
+  for (uint32_t slot = blockIdx.x - 1; slot < n_slots; slot += gridDim.x - 1) {
+    block_scan_4096(sort_hist2(sc) + (size_t)slot * kSortBins, s_scan);
+    __syncthreads();  // s_scan is reused by the next slot
+  }
+}
+
+__global__ void __launch_bounds__(256) k_sort_place(const uint32_t* __restrict__ keys, const KeysArgs* __restrict__ a, int n_val,
+                                                    SortScratch* __restrict__ sc, uint32_t* __restrict__ order) {
+  const int n = a ? a->n : n_val;
+  const int lane = threadIdx.x & 31;
+  uint32_t* hist2 = sort_hist2(sc);
+  for (int i0 = (blockIdx.x * blockDim.x + threadIdx.x) - lane; i0 < n; i0 += gridDim.x * blockDim.x) {
+    const int i = i0 + lane;
+    const unsigned act = __ballot_sync(0xFFFFFFFFu, i < n);
+    if (i >= n) continue;
+    const uint32_t key = keys[i];
+    const uint32_t cube = key >> 12;
+    const unsigned pk = __match_any_sync(act, key);
+    const int leader = __ffs(pk) - 1;
+    uint32_t base = 0;
+    if (lane == leader) {
+      const uint32_t slot = sc->slot_of[cube] - 1u;
+      base = sc->start[cube] + atomicAdd(&hist2[(size_t)slot * kSortBins + (key & kSortLowMask)], (uint32_t)__popc(pk));
+    }
+    base = __shfl_sync(pk, base, leader);
+    order[base + __popc(pk & ((1u << lane) - 1u))] = (uint32_t)i;
+  }
+}
+
+// zero what the sort touched: slot_of[] and the level-2 counters of the slots in use (hist1 was zeroed by k_sort_scan)
+__global__ void __launch_bounds__(256) k_sort_clear(SortScratch* __restrict__ sc) {
+  const uint32_t n_slots = sc->n_slots;
+  uint4* h = reinterpret_cast<uint4*>(sort_hist2(sc));
+  const size_t total = (size_t)n_slots * (kSortBins / 4);
+  for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) h[e] = make_uint4(0u, 0u, 0u, 0u);
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < kSortBins; e += gridDim.x * blockDim.x) sc->slot_of[e] = 0;
+  __syncthreads();
+  // n_slots is reset by the LAST block (every block has read it by then)
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) s_last = atomicAdd(&sc->pad[0], 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    sc->n_slots = 0;
+    sc->pad[0] = 0;
   }
 }
 
@@ -144,7 +281,8 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
                                                                int n, StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
                                                                float* __restrict__ nn_d2, int* __restrict__ nn_cnt,
                                                                uint32_t* __restrict__ ctr, uint32_t* __restrict__ left,
-                                                               const IekfCtl* __restrict__ ctl, uint32_t* __restrict__ stats) {
+                                                               const IekfCtl* __restrict__ ctl, uint32_t* __restrict__ stats,
+                                                               uint4* __restrict__ prof_out) {
   __shared__ TileSmem smem[kTileWarps];
   __shared__ StateArg s_st;
   if (DEV && (ctl->finished || !ctl->converge)) return;  // cached neighbours are reused (ekfom_data.converge == false)
@@ -169,6 +307,8 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
       if (XFORM) body_to_world(st, b.x, b.y, b.z, qx, qy, qz);
     }
     unsigned overflow = 0;
+    TileProf prof{0, 0, 0};
+    const long long t0 = prof_out ? clock64() : 0;
     const unsigned pending = tile_search(m, sm, lane, qx, qy, qz, valid, max_d2, [&](const Top32& L, int cnt) {
       cnt = min(cnt, k);
       const uint32_t ks[kK] = {L.b0, L.b1, L.b2, L.b3, L.b4};
@@ -181,7 +321,10 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
           if (nn_d2) nn_d2[(size_t)i * k + j] = have ? __uint_as_float(ks[j]) : inf;
         }
       nn_cnt[i] = cnt;
-    }, &overflow);
+    }, &overflow, prof_out ? &prof : nullptr);
+    if (prof_out && lane == 0)
+      prof_out[tile] = make_uint4((uint32_t)(clock64() - t0), (uint32_t)prof.passes | ((uint32_t)__popc(pending) << 8) | ((uint32_t)__popc(overflow) << 16),
+                                  (uint32_t)prof.staged, (uint32_t)prof.cells);
     if (pending) {  // defer to k_knn_left
       if (lane == 0 && stats) {  // [1] staging overflow / growth limit, [2] tile too incoherent (beyond kTileMaxSub sub-tiles)
         if (overflow) atomicAdd(stats + 1, (uint32_t)__popc(overflow));
@@ -768,6 +911,8 @@ int scan_alloc(lio_ctx* c) {
       LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_hilbert, &hil, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
       LIO_CUDA(cudaStreamSynchronize(c->stream));
     }
+    e = getenv("LIO_TILE_PROF");  // per-tile cycle / pass counters of the last scan search (lio_tile_profile)
+    if (e && std::strcmp(e, "1") == 0) LIO_CUDA(cudaMalloc(&c->tile_prof, sizeof(uint4) * ((n + 31) / 32 + 1)));
     e = getenv("LIO_BATCH_LEFT");
     c->batch_left_warp = (e && std::strcmp(e, "warp") == 0) ? 1 : 0;
     e = getenv("LIO_SORT_GRAPH");
@@ -807,7 +952,8 @@ void scan_free(lio_ctx* c) {
   cudaFree(c->list_nodown);
   cudaFree(c->partials);
   cudaFree(c->tile_stats);
-  cudaFree(c->tile_tmp);
+  cudaFree(c->sort_scratch);
+  cudaFree(c->tile_prof);
   for (int j = 0; j < 2; ++j) {
     cudaFree(c->tile_keys[j]);
     cudaFree(c->tile_vals[j]);
@@ -845,7 +991,12 @@ int scan_undistort(lio_ctx* c, const float* t_ms_host, const double* pose_host, 
   return LIO_OK;
 }
 
+constexpr size_t kSortScratchBytes = sizeof(SortScratch) + sizeof(uint32_t) * (size_t)kSortBins * kSortBins;  // 64 MB of level-2 counters
 int tile_ensure(lio_ctx* c, uint32_t n) {
+  if (!c->sort_scratch) {
+    LIO_CUDA(cudaMalloc(&c->sort_scratch, kSortScratchBytes));
+    LIO_CUDA(cudaMemsetAsync(c->sort_scratch, 0, kSortScratchBytes, c->stream));
+  }
   if (n <= c->tile_cap) return LIO_OK;
   for (auto& g : c->sort_graphs) cudaGraphExecDestroy((cudaGraphExec_t)g.second);  // they captured the old buffers
   c->sort_graphs.clear();
@@ -854,43 +1005,41 @@ int tile_ensure(lio_ctx* c, uint32_t n) {
     cudaFree(c->tile_vals[j]);
     c->tile_keys[j] = c->tile_vals[j] = nullptr;
   }
-  cudaFree(c->tile_tmp);
-  c->tile_tmp = nullptr;
   c->tile_cap = 0;
   const uint32_t cap = n + n / 8 + 1024;
-  for (int j = 0; j < 2; ++j) {
-    LIO_CUDA(cudaMalloc(&c->tile_keys[j], sizeof(uint32_t) * cap));
-    LIO_CUDA(cudaMalloc(&c->tile_vals[j], sizeof(uint32_t) * cap));
-  }
-  size_t bytes = 0;
-  LIO_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0], c->tile_vals[1], (int)cap, 0, kTileKeyBits,
-                                           c->stream));
-  LIO_CUDA(cudaMalloc(&c->tile_tmp, bytes));
-  c->tile_tmp_bytes = bytes;
+  LIO_CUDA(cudaMalloc(&c->tile_keys[0], sizeof(uint32_t) * cap));  // keys
+  for (int j = 0; j < 2; ++j) LIO_CUDA(cudaMalloc(&c->tile_vals[j], sizeof(uint32_t) * cap));  // [0] leftover list, [1] order
   c->tile_cap = cap;
   c->order_valid = false;
   return LIO_OK;
 }
 
-// tile order (sorted curve keys) of n query points (body points at `st` when xform) -> c->tile_vals[1]
+// the sort kernels on c->stream: keys -> tile_keys[0], order -> tile_vals[1].  `args` non-null: graph form (state and n read
+// from the device block).
+static void sort_launch(lio_ctx* c, const float4* pts, int n_grid, const KeysArgs* args, const StateArg& st, int n, bool xform) {
+  SortScratch* sc = (SortScratch*)c->sort_scratch;
+  const int grid = std::max(1, std::min((n_grid + 255) / 256, c->n_sms * 8));
+  if (xform)
+    k_sort_count<true><<<grid, 256, 0, c->stream>>>(c->map, pts, args, st, n, c->tile_keys[0], sc);
+  else
+    k_sort_count<false><<<grid, 256, 0, c->stream>>>(c->map, pts, args, st, n, c->tile_keys[0], sc);
+  k_sort_scan<<<1 + c->n_sms * 3, kSortScanBlock, 0, c->stream>>>(sc);  // block 0: level 1; the others stride over the slots in use
+  k_sort_place<<<grid, 256, 0, c->stream>>>(c->tile_keys[0], args, n, sc, c->tile_vals[1]);
+  k_sort_clear<<<c->n_sms * 2, 256, 0, c->stream>>>(sc);
+  c->launches += 4;
+}
+
+// tile order (curve order) of n query points (body points at `st` when xform) -> c->tile_vals[1]
 static int tile_order(lio_ctx* c, const float4* pts, int n, const StateArg& st, bool xform) {
   int rc = tile_ensure(c, (uint32_t)n);
   if (rc) return rc;
-  const int grid = std::max(1, std::min((n + 255) / 256, c->n_sms * 8));
-  if (xform)
-    k_tile_keys<true><<<grid, 256, 0, c->stream>>>(c->map, pts, n, st, c->tile_keys[0], c->tile_vals[0]);
-  else
-    k_tile_keys<false><<<grid, 256, 0, c->stream>>>(c->map, pts, n, st, c->tile_keys[0], c->tile_vals[0]);
-  size_t bytes = c->tile_tmp_bytes;
-  LIO_CUDA(cub::DeviceRadixSort::SortPairs(c->tile_tmp, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0], c->tile_vals[1], n, 0, kTileKeyBits,
-                                           c->stream));
-  c->launches += 1;  // + the library's sort passes (not ours)
+  sort_launch(c, pts, n, nullptr, st, n, xform);
+  LIO_CUDA(cudaGetLastError());
   return LIO_OK;
 }
 
-// Scan ordering through a captured graph: the keys kernel and the radix-sort passes cost ~45 us of device time but ~110 us
-// when launched one by one (the library queries kernel attributes on every call and the tiny passes leave the GPU waiting
-// for the host); as one graph launch the passes run back to back.  Graphs are cached per padded size (multiples of 8192).
+// Scan ordering through a captured graph (one launch for the argument copy + the three kernels).  Graphs are cached per padded
+// size (multiples of 8192); the true size and the state sit in a small device block refreshed by the graph's memcpy node.
 static int tile_order_graph(lio_ctx* c, int n, const double* state_host) {
   int rc = tile_ensure(c, (uint32_t)n);
   if (rc) return rc;
@@ -906,13 +1055,12 @@ static int tile_order_graph(lio_ctx* c, int n, const double* state_host) {
     cudaGraph_t graph = nullptr;
     LIO_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeRelaxed));
     cudaMemcpyAsync(c->keys_args_dev, c->keys_args_host, sizeof(KeysArgs), cudaMemcpyHostToDevice, c->stream);
-    const int grid = std::max(1, std::min((n_pad + 255) / 256, c->n_sms * 8));
-    k_tile_keys_g<<<grid, 256, 0, c->stream>>>(c->map, c->body, (const KeysArgs*)c->keys_args_dev, n_pad, c->tile_keys[0], c->tile_vals[0]);
-    size_t bytes = c->tile_tmp_bytes;
-    const cudaError_t se = cub::DeviceRadixSort::SortPairs(c->tile_tmp, bytes, c->tile_keys[0], c->tile_keys[1], c->tile_vals[0],
-                                                           c->tile_vals[1], n_pad, 0, kTileKeyBits, c->stream);
+    const int64_t l0 = c->launches;
+    StateArg unused{};
+    sort_launch(c, c->body, n_pad, (const KeysArgs*)c->keys_args_dev, unused, 0, true);
+    c->launches = l0;
     const cudaError_t ce = cudaStreamEndCapture(c->stream, &graph);
-    if (se != cudaSuccess || ce != cudaSuccess || !graph) {
+    if (ce != cudaSuccess || !graph) {
       if (graph) cudaGraphDestroy(graph);
       cudaGetLastError();
       c->sort_graph_ok = false;  // fall back to plain launches for the rest of this context's life
@@ -931,7 +1079,7 @@ static int tile_order_graph(lio_ctx* c, int n, const double* state_host) {
   std::memcpy(a->s, state_host, sizeof(a->s));
   a->n = n;
   LIO_CUDA(cudaGraphLaunch(exec, c->stream));
-  c->launches += 1;  // our keys kernel (+ the library's sort passes)
+  c->launches += 4;
   return LIO_OK;
 }
 
@@ -958,12 +1106,12 @@ int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
     c->tile_flip ^= 1;
     if (dev_loop) {
       k_knn_tile<true, true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
-                                                                                  c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], c->iekf_ctl, c->tile_stats);
+                                                                                  c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], c->iekf_ctl, c->tile_stats, c->tile_prof);
       k_knn_left<true, true><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
                                                                          c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, c->iekf_ctl);
     } else {
       k_knn_tile<true, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
-                                                                                   c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats);
+                                                                                   c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats, c->tile_prof);
       k_knn_left<true, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
                                                                           c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, nullptr);
     }
@@ -991,7 +1139,7 @@ int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float
     uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
     c->tile_flip ^= 1;
     k_knn_tile<false, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, q_dev, c->tile_vals[1], n, st, k, max_d2, out_nn,
-                                                                                  out_d2, out_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats);
+                                                                                  out_d2, out_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats, nullptr);
     if (c->batch_left_warp)
       k_knn_left<false, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
                                                                          ctr, ctr_next, c->tile_stats, nullptr);

@@ -146,6 +146,10 @@ int lio_knn_stats(lio_ctx* ctx, uint64_t* fallback_queries);
 /* out4: [0] queries finished by the per-query kernel, [1] of those deferred because a tile's staging area or growth limit
  * overflowed, [2] deferred because the tile was too incoherent, [3] reserved.  Running totals since context creation. */
 int lio_knn_stats_detail(lio_ctx* ctx, uint64_t* out4);
+/* Per-tile counters of the last scan search (context created with LIO_TILE_PROF=1 in the environment): 4 words per tile of
+ * 32 curve-ordered queries = {SM cycles, staging passes | deferred queries << 8 | overflowed << 16, staged points, cells
+ * probed}.  Copies min(cap_tiles, tiles) records; *n_tiles = tiles of the current scan. */
+int lio_tile_profile(lio_ctx* ctx, uint32_t* out4, int cap_tiles, int* n_tiles);
 /* Achievable random-gather bandwidth of the device: random 16-byte loads from a table of `table_bytes` (use >= 320 MB so
  * it exceeds L2).  *gbps_16B counts the 16 requested bytes per load, *gbps_sector the 32-byte sectors they drag. */
 int lio_gather_probe(lio_ctx* ctx, uint64_t table_bytes, int reps, double* gbps_16B, double* gbps_sector);
