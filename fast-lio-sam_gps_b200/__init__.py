@@ -101,6 +101,8 @@ LIO_SYMBOLS = {
     "lio_timing_reset": (C.c_int, [C.c_void_p]),
     "lio_knn_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "lio_knn_stats_detail": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "lio_map_compact": (C.c_int, [C.c_void_p, C.c_int]),
+    "lio_map_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "lio_tile_profile": (C.c_int, [C.c_void_p, _u32p, C.c_int, _i32p]),
     "lio_gather_probe": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "lio_launch_count": (C.c_int64, [C.c_void_p]),
@@ -334,11 +336,21 @@ class LioContext:
         self._check(self.lib.lio_knn_stats_detail(self.h, v))
         return dict(per_query=int(v[0]), overflow=int(v[1]), incoherent=int(v[2]))
 
+    def map_compact(self, renumber=False):
+        """Rebuild the store from its live points (reclaims cells / buckets emptied by box deletes)."""
+        self._check(self.lib.lio_map_compact(self.h, 1 if renumber else 0))
+
+    def map_stats(self):
+        v = (C.c_uint64 * 8)()
+        self._check(self.lib.lio_map_stats(self.h, v))
+        return dict(live=int(v[0]), next_id=int(v[1]), pool_top=int(v[2]), pool_cap=int(v[3]), n_cells=int(v[4]), cell_limit=int(v[5]),
+                    error=int(v[6]), dead_since_compact=int(v[7]))
+
     def tile_profile(self):
-        """(tiles, 4) uint32 per-tile counters of the last scan search (needs LIO_TILE_PROF=1 at context creation)."""
+        """(tiles, 8) uint32 per-tile counters of the last scan search (needs LIO_TILE_PROF=1 at context creation)."""
         n = C.c_int(0)
         self._check(self.lib.lio_tile_profile(self.h, None, 0, C.byref(n)))
-        out = np.zeros((max(n.value, 1), 4), np.uint32)
+        out = np.zeros((max(n.value, 1), 8), np.uint32)
         self._check(self.lib.lio_tile_profile(self.h, _p(out, _u32p), n.value, C.byref(n)))
         return out[: n.value]
 

@@ -231,12 +231,34 @@ int lio_map_delete_boxes(lio_ctx* c, const float* boxes, int nb, int* n_deleted)
   if (nb == 0) return LIO_OK;
   rc = map_delete_boxes(c, boxes, nb);
   if (rc) return rc;
-  if (n_deleted) {
-    MapCounters ctr;
-    rc = map_read_counters(c, &ctr);
-    if (rc) return rc;
-    *n_deleted = (int)ctr.deleted;
+  if (n_deleted) *n_deleted = (int)c->last_deleted;
+  return LIO_OK;
+}
+
+int lio_map_compact(lio_ctx* c, int renumber_ids) {
+  int rc = check_ctx(c);
+  if (rc) return rc;
+  return map_compact(c, renumber_ids != 0);
+}
+
+int lio_map_stats(lio_ctx* c, uint64_t* out8) {
+  int rc = check_ctx(c);
+  if (rc) return rc;
+  if (!out8) {
+    set_error("null output");
+    return LIO_E_ARG;
   }
+  MapCounters ctr;
+  LIO_CUDA(cudaMemcpyAsync(&ctr, c->map.ctr, sizeof(MapCounters), cudaMemcpyDeviceToHost, c->stream));
+  LIO_CUDA(cudaStreamSynchronize(c->stream));
+  out8[0] = ctr.live > 0 ? (uint64_t)ctr.live : 0;
+  out8[1] = ctr.next_id;
+  out8[2] = ctr.pool_top;
+  out8[3] = c->map.pool_cap;
+  out8[4] = ctr.n_cells;
+  out8[5] = c->map.cell_limit;
+  out8[6] = ctr.error;
+  out8[7] = c->dead_since_compact;
   return LIO_OK;
 }
 
@@ -560,6 +582,8 @@ static int iekf_common(lio_ctx* c, double* state, double* P, double R, int max_i
     set_error("no scan uploaded");
     return LIO_E_STATE;
   }
+  rc = map_check_health(c);  // what the previous scan's inserts left in the mapped status word (capacity error, ids running out)
+  if (rc) return rc;
   // default: host loop over lio_h_share (one mapped-memory poll per iteration, ~12 us; measured 0.53 ms/scan on B200).
   // LIO_IEKF_MODE=device enqueues the whole loop on the device (lio_iekf.cuh: no host round trip, but the 23x23 FP64
   // algebra then runs in one thread block, ~60 us per iteration -> 0.79 ms/scan): kept as a tested alternative.
@@ -723,18 +747,21 @@ int lio_knn_stats_detail(lio_ctx* c, uint64_t* out4) {
   return LIO_OK;
 }
 
-int lio_tile_profile(lio_ctx* c, uint32_t* out4, int cap_tiles, int* n_tiles) {
+int lio_tile_profile(lio_ctx* c, uint32_t* out8, int cap_tiles, int* n_tiles) {
   int rc = check_ctx(c);
   if (rc) return rc;
   if (!c->tile_prof) {
     set_error("lio_tile_profile: create the context with LIO_TILE_PROF=1");
     return LIO_E_STATE;
   }
-  const int tiles = (c->scan_n + 31) / 32;
+  uint32_t tasks = 0;
+  rc = tile_tasks_of_last_search(c, &tasks);
+  if (rc) return rc;
+  const int tiles = (int)std::min(tasks, c->tile_prof_cap);
   if (n_tiles) *n_tiles = tiles;
   const int m = std::min(tiles, cap_tiles);
-  if (out4 && m > 0) {
-    LIO_CUDA(cudaMemcpyAsync(out4, c->tile_prof, sizeof(uint4) * (size_t)m, cudaMemcpyDeviceToHost, c->stream));
+  if (out8 && m > 0) {
+    LIO_CUDA(cudaMemcpyAsync(out8, c->tile_prof, sizeof(uint4) * 2 * (size_t)m, cudaMemcpyDeviceToHost, c->stream));
     LIO_CUDA(cudaStreamSynchronize(c->stream));
   }
   return LIO_OK;

@@ -60,6 +60,11 @@ struct lio_ctx {
   unsigned long long* vox_best = nullptr;
   uint32_t vox_cap = 0;
   float* boxes_dev = nullptr;  // up to 64 boxes
+  uint32_t* map_err_host = nullptr;  // mapped pinned word: MapCounters::error | kWarnIdsHigh, written by the last kernel of every add
+  uint32_t* map_err_dev = nullptr;
+  uint64_t dead_since_compact = 0;   // points removed by delete_boxes since the last compaction
+  uint32_t last_deleted = 0;         // points removed by the last delete_boxes
+  bool auto_compact = true;          // LIO_MAP_COMPACT=0 disables the automatic compaction after a box delete
 
   // scan
   int scan_n = 0;
@@ -82,9 +87,13 @@ struct lio_ctx {
   // tile kNN: curve order of the scan (lio_knn_tile.cuh)
   uint32_t* tile_keys[2] = {nullptr, nullptr};
   uint32_t* tile_vals[2] = {nullptr, nullptr};
+  float4* tile_sorted = nullptr;             // the query points in curve order (k_sort_place)
+  unsigned long long* tile_queue = nullptr;  // 2 * tile_cap pushed (tile << 32 | lane mask) tasks; a slot is zeroed by its taker
+  uint32_t tile_prof_cap = 0;                // tickets recorded by LIO_TILE_PROF
   void* sort_scratch = nullptr;  // SortScratch (lio_scan.cu): coarse-bin histogram / offsets / cursors of the scan ordering
   uint32_t tile_cap = 0;
   bool order_valid = false;      // tile_vals[1] holds the order of the current scan
+  bool resort_each_search = true;  // the curve order is recomputed at the state of every search (LIO_RESORT=0: once per scan)
   std::vector<std::pair<int, void*>> sort_graphs;  // (padded size, cudaGraphExec_t) of the captured keys + sort passes
   bool sort_graph_ok = true;     // false after a failed capture (LIO_SORT_GRAPH=0 disables it up front)
   void* keys_args_host = nullptr;  // pinned KeysArgs staged by the graph's memcpy node
@@ -151,6 +160,8 @@ int map_add_device(lio_ctx* c, const float4* pts, uint32_t n_max, const uint32_t
 int map_delete_boxes(lio_ctx* c, const float* boxes_host, int nb);
 int map_read_counters(lio_ctx* c, MapCounters* out);
 int map_export(lio_ctx* c, std::vector<float4>& out);
+int map_compact(lio_ctx* c, bool renumber);
+int map_check_health(lio_ctx* c);  // sticky capacity error -> LIO_E_CAPACITY; ids running out -> compaction with renumbering
 
 // scan / measurement (lio_scan.cu)
 int scan_alloc(lio_ctx* c);
@@ -164,6 +175,7 @@ int iekf_update_device(lio_ctx* c, double* state, double* P, double R, int max_i
 int scan_undistort(lio_ctx* c, const float* t_ms_host, const double* pose_host, int n_pose, const double* end_state);
 int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float4* out_nn, float* out_d2, int* out_cnt);
 int tile_ensure(lio_ctx* c, uint32_t n);
+int tile_tasks_of_last_search(lio_ctx* c, uint32_t* n_tasks);
 
 // timing helpers (lio_capi.cu)
 void timer_begin(lio_ctx* c, int id);

@@ -17,11 +17,14 @@ namespace lio {
 constexpr uint32_t kEmptyId = 0xFFFFFFFFu;
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr unsigned long long kEmptyKey = ~0ull;
+constexpr unsigned long long kPendingKey = ~0ull - 1ull;  // entry being created (insert kernels only; real keys use 63 bits)
 constexpr int kSlots = 8;  // points per bucket
 constexpr int kK = 5;      // NUM_MATCH_POINTS
 
 constexpr uint32_t kErrHashFull = 1u;
 constexpr uint32_t kErrPoolFull = 2u;
+constexpr uint32_t kWarnIdsHigh = 4u;              // host-visible only: the 32-bit insertion counter is three quarters used
+constexpr uint32_t kIdRenumberAt = 0xC0000000u;  // -> the next API call compacts the store and renumbers the ids by rank
 
 struct __align__(16) HashEntry {
   unsigned long long key;
@@ -47,9 +50,10 @@ struct MapCounters {
 struct MapView {
   HashEntry* table;
   uint32_t mask;  // capacity - 1
+  uint32_t cell_limit;  // occupied entries never exceed this (capacity / 2): read-only probes always terminate
   float4* slots;  // pool_cap * kSlots
   uint32_t* next; // pool_cap
-  uint32_t pool_cap;
+  uint32_t pool_cap;  // buckets; bucket index pool_cap is the always-empty null bucket
   MapCounters* ctr;
   float ds;        // filter_size_map
   int cell_shift;  // log2(cell_mult)

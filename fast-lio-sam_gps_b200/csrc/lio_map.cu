@@ -39,19 +39,33 @@ __global__ void k_cells_ensure(MapView m, const float4* __restrict__ pts, uint32
     const unsigned long long key = pack3(cx, cy, cz);
     uint32_t s = hash64(key) & m.mask;
     uint32_t found = kNone;
-    for (uint32_t probes = 0; probes <= m.mask; ++probes) {
+    bool pool_fail = false, table_fail = false;
+    for (uint32_t probes = 0; probes <= m.mask;) {
       unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&m.table[s].key);
-      if (cur == kEmptyKey) cur = atomicCAS(&m.table[s].key, kEmptyKey, key);
-      if (cur == kEmptyKey) {  // this thread created the cell: give it a head bucket
+      if (cur == kEmptyKey) cur = atomicCAS(&m.table[s].key, kEmptyKey, kPendingKey);
+      if (cur == kPendingKey) continue;  // another thread is creating a cell here: its key (or "empty" again) appears shortly
+      if (cur == kEmptyKey) {
+        // this thread owns the entry until it publishes the key.  Occupied entries never exceed cell_limit (capacity / 2):
+        // a read-only probe (table_find and the search kernels' own probe loops) always meets an empty entry and terminates.
+        if (atomicAdd(&m.ctr->n_cells, 1u) >= m.cell_limit) {
+          atomicSub(&m.ctr->n_cells, 1u);
+          atomicExch(&m.table[s].key, kEmptyKey);
+          table_fail = true;
+          break;
+        }
         uint32_t b = atomicAdd(&m.ctr->pool_top, 1u);
         if (b >= m.pool_cap) {
+          // pool exhausted: the cell points at the null bucket (index pool_cap: always empty, never written), readers see an
+          // empty cell, writers refuse (claim_slot_g), the sticky error reaches the host with the next result
           atomicOr(&m.ctr->error, kErrPoolFull);
-          b = 0;
+          b = m.pool_cap;
+          pool_fail = true;
         }
         m.table[s].head = b;
-        atomicAdd(&m.ctr->n_cells, 1u);
         atomicOr(&m.occ[occ_word_of(m, cx >> 2, cy >> 2, cz >> 2)], 1ull << occ_bit_of(cx, cy, cz));
-        found = s;
+        __threadfence();
+        atomicExch(&m.table[s].key, key);  // publish
+        found = pool_fail ? kNone : s;
         break;
       }
       if (cur == key) {
@@ -59,61 +73,11 @@ __global__ void k_cells_ensure(MapView m, const float4* __restrict__ pts, uint32
         break;
       }
       s = (s + 1) & m.mask;
+      ++probes;
     }
-    if (found == kNone) atomicOr(&m.ctr->error, kErrHashFull);
+    if (found == kNone && !pool_fail) atomicOr(&m.ctr->error, kErrHashFull);
+    (void)table_fail;
     ent[i] = found;
-  }
-}
-
-// claim a free slot in the chain of hash entry `ei` and store the point there
-__device__ bool claim_slot(const MapView& m, uint32_t ei, float x, float y, float z, uint32_t id) {
-  HashEntry* e = m.table + ei;
-  const uint32_t head = e->head;
-  uint32_t b = head, spare = kNone;
-  while (true) {
-    float4* s = m.slots + (size_t)b * kSlots;
-#pragma unroll
-    for (int j = 0; j < kSlots; ++j) {
-      uint32_t* w = reinterpret_cast<uint32_t*>(&s[j].w);
-      if (*reinterpret_cast<volatile uint32_t*>(w) == kEmptyId && atomicCAS(w, kEmptyId, id) == kEmptyId) {
-        s[j].x = x;
-        s[j].y = y;
-        s[j].z = z;
-        return true;
-      }
-    }
-    uint32_t* link = (b == head) ? &e->ovf : &m.next[b];
-    uint32_t nb = *reinterpret_cast<volatile uint32_t*>(link);
-    if (nb == kNone) {
-      if (spare == kNone) {
-        spare = atomicAdd(&m.ctr->pool_top, 1u);
-        if (spare >= m.pool_cap) {
-          atomicOr(&m.ctr->error, kErrPoolFull);
-          return false;
-        }
-      }
-      const uint32_t prev = atomicCAS(link, kNone, spare);
-      if (prev == kNone) {
-        nb = spare;
-        spare = kNone;
-      } else {
-        nb = prev;  // somebody else linked first; keep the spare for the next tail
-      }
-    }
-    b = nb;
-  }
-}
-
-// ---- Add_Points(points, false) -----------------------------------------------------------------
-__global__ void k_insert_plain(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
-                               const uint32_t* __restrict__ ent) {
-  const uint32_t n = batch_n(n_max, n_dev);
-  const uint32_t base = m.ctr->next_id;
-  for (uint32_t i = spread_index(); i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t ei = ent[i];
-    if (ei == kNone) continue;
-    const float4 p = pts[i];
-    if (claim_slot(m, ei, p.x, p.y, p.z, base + i)) atomicAdd(&m.ctr->live, 1);
   }
 }
 
@@ -123,104 +87,6 @@ __device__ __forceinline__ void voxel_centre(int kx, int ky, int kz, float ds, f
   mx = minx + (maxx - minx) / 2.0f;
   my = miny + (maxy - miny) / 2.0f;
   mz = minz + (maxz - minz) / 2.0f;
-}
-
-// ---- Add_Points(points, true), phase "scan" (read-only on the point store) ----------------------
-__global__ void k_ds_scan(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
-                          const uint32_t* __restrict__ ent, unsigned long long* vox_keys, unsigned long long* vox_best,
-                          uint32_t vox_mask, uint32_t* __restrict__ tslot, unsigned long long* __restrict__ ebest,
-                          uint32_t* __restrict__ ecnt) {
-  const uint32_t n = batch_n(n_max, n_dev);
-  for (uint32_t i = spread_index(); i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t ei = ent[i];
-    tslot[i] = kNone;
-    if (ei == kNone) continue;
-    const float4 p = pts[i];
-    const int kx = vox_of(p.x, m.ds), ky = vox_of(p.y, m.ds), kz = vox_of(p.z, m.ds);
-    float mx, my, mz;
-    voxel_centre(kx, ky, kz, m.ds, mx, my, mz);
-    // best existing point of this voxel
-    unsigned long long best = ~0ull;
-    uint32_t cnt = 0;
-    const HashEntry e = m.table[ei];
-    for (uint32_t b = e.head; b != kNone; b = chain_next(m, e.head, e.ovf, b)) {
-      const float4* s = m.slots + (size_t)b * kSlots;
-#pragma unroll
-      for (int j = 0; j < kSlots; ++j) {
-        const float4 q = s[j];
-        const uint32_t id = __float_as_uint(q.w);
-        if (id == kEmptyId) continue;
-        if (vox_of(q.x, m.ds) != kx || vox_of(q.y, m.ds) != ky || vox_of(q.z, m.ds) != kz) continue;
-        ++cnt;
-        const unsigned long long k = key64(sqdist3(q.x, q.y, q.z, mx, my, mz), id);
-        if (k < best) best = k;
-      }
-    }
-    ebest[i] = best;
-    ecnt[i] = cnt;
-    // batch arbitration: min distance, ties -> the LATER batch point
-    const unsigned long long vkey = pack3(kx, ky, kz);
-    uint32_t s = hash64(vkey) & vox_mask;
-    while (true) {
-      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&vox_keys[s]);
-      if (cur == kEmptyKey) cur = atomicCAS(&vox_keys[s], kEmptyKey, vkey);
-      if (cur == kEmptyKey || cur == vkey) break;
-      s = (s + 1) & vox_mask;
-    }
-    const float d = sqdist3(p.x, p.y, p.z, mx, my, mz);
-    atomicMin(&vox_best[s], ((unsigned long long)__float_as_uint(d) << 32) | (0xFFFFFFFFu - i));
-    tslot[i] = s;
-  }
-}
-
-// remove the pre-existing points of voxel (kx,ky,kz) from the chain of entry e, except `keep`
-__device__ void erase_voxel(const MapView& m, const HashEntry& e, int kx, int ky, int kz, uint32_t base_id, uint32_t keep) {
-  for (uint32_t b = e.head; b != kNone; b = chain_next(m, e.head, e.ovf, b)) {
-    float4* s = m.slots + (size_t)b * kSlots;
-#pragma unroll
-    for (int j = 0; j < kSlots; ++j) {
-      uint32_t* w = reinterpret_cast<uint32_t*>(&s[j].w);
-      const uint32_t id = *reinterpret_cast<volatile uint32_t*>(w);
-      if (id == kEmptyId || id >= base_id || id == keep) continue;  // only points that predate this batch
-      const float x = *reinterpret_cast<volatile float*>(&s[j].x), y = *reinterpret_cast<volatile float*>(&s[j].y),
-                  z = *reinterpret_cast<volatile float*>(&s[j].z);
-      if (vox_of(x, m.ds) != kx || vox_of(y, m.ds) != ky || vox_of(z, m.ds) != kz) continue;
-      atomicCAS(w, id, kEmptyId);  // a slot that was recycled meanwhile carries another id and is left alone
-    }
-  }
-}
-
-// ---- Add_Points(points, true), phase "commit" ---------------------------------------------------
-__global__ void k_ds_commit(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
-                            const uint32_t* __restrict__ ent, const unsigned long long* __restrict__ vox_best,
-                            const uint32_t* __restrict__ tslot, const unsigned long long* __restrict__ ebest,
-                            const uint32_t* __restrict__ ecnt) {
-  const uint32_t n = batch_n(n_max, n_dev);
-  const uint32_t base = m.ctr->next_id;
-  for (uint32_t i = spread_index(); i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t ts = tslot[i];
-    if (ts == kNone) continue;
-    const float4 p = pts[i];
-    const int kx = vox_of(p.x, m.ds), ky = vox_of(p.y, m.ds), kz = vox_of(p.z, m.ds);
-    float mx, my, mz;
-    voxel_centre(kx, ky, kz, m.ds, mx, my, mz);
-    const uint32_t dbits = __float_as_uint(sqdist3(p.x, p.y, p.z, mx, my, mz));
-    if (vox_best[ts] != (((unsigned long long)dbits << 32) | (0xFFFFFFFFu - i))) continue;  // not the voxel's winner
-    const uint32_t ei = ent[i];
-    const HashEntry e = m.table[ei];
-    const unsigned long long eb = ebest[i];
-    const uint32_t ec = ecnt[i];
-    if (ec == 0 || dbits <= (uint32_t)(eb >> 32)) {
-      if (ec) erase_voxel(m, e, kx, ky, kz, base, kEmptyId);
-      if (claim_slot(m, ei, p.x, p.y, p.z, base + i)) {
-        atomicAdd(&m.ctr->live, 1 - (int)ec);
-        atomicAdd(&m.ctr->batch_alive, 1u);
-      }
-    } else if (ec > 1) {
-      erase_voxel(m, e, kx, ky, kz, base, (uint32_t)eb);
-      atomicAdd(&m.ctr->live, -(int)(ec - 1));
-    }
-  }
 }
 
 // ---- 8-lane group forms: lane j of a group looks at slot j of a bucket, so a bucket is ONE coalesced 128-byte access
@@ -244,7 +110,8 @@ __device__ __forceinline__ uint32_t groups_total() { return gridDim.x * (blockDi
 // claim a free slot in the chain of entry `ei` for point (x,y,z,id); every lane of the group returns the outcome
 __device__ bool claim_slot_g(const MapView& m, const Grp& g, uint32_t ei, float x, float y, float z, uint32_t id) {
   HashEntry* e = m.table + ei;
-  const uint32_t head = e->head;
+  const uint32_t head = *reinterpret_cast<volatile uint32_t*>(&e->head);
+  if (head >= m.pool_cap) return false;  // cell created while the pool was exhausted (null bucket): error already flagged
   uint32_t b = head, spare = kNone;
   while (true) {
     float4* s = m.slots + (size_t)b * kSlots;
@@ -296,6 +163,8 @@ __device__ bool claim_slot_g(const MapView& m, const Grp& g, uint32_t ei, float 
   }
 }
 
+// IDS_IN_W: the batch carries its ids in .w (map_compact re-inserting the live points under their old ids)
+template <bool IDS_IN_W>
 __global__ void __launch_bounds__(256) k_insert_plain_g(MapView m, const float4* __restrict__ pts, uint32_t n_max, const uint32_t* n_dev,
                                                         const uint32_t* __restrict__ ent) {
   const Grp g;
@@ -305,7 +174,8 @@ __global__ void __launch_bounds__(256) k_insert_plain_g(MapView m, const float4*
     const uint32_t ei = ent[i];
     if (ei == kNone) continue;
     const float4 p = pts[i];
-    if (claim_slot_g(m, g, ei, p.x, p.y, p.z, base + i) && g.gl == 0) atomicAdd(&m.ctr->live, 1);
+    const uint32_t id = IDS_IN_W ? __float_as_uint(p.w) : base + i;
+    if (claim_slot_g(m, g, ei, p.x, p.y, p.z, id) && g.gl == 0) atomicAdd(&m.ctr->live, 1);
   }
 }
 
@@ -409,9 +279,14 @@ __global__ void __launch_bounds__(256) k_ds_commit_g(MapView m, const float4* __
   }
 }
 
-__global__ void k_advance_ids(MapCounters* ctr, uint32_t n_max, const uint32_t* n_dev) {
+// last kernel of every add: advances the id counter and mirrors the sticky error word (plus the "ids running out" warning)
+// into mapped host memory, where the next API call sees it without a device read
+__global__ void k_advance_ids(MapCounters* ctr, uint32_t n_max, const uint32_t* n_dev, uint32_t* __restrict__ err_host) {
   ctr->next_id += batch_n(n_max, n_dev);
+  const uint32_t w = ctr->error | (ctr->next_id > kIdRenumberAt ? kWarnIdsHigh : 0u);
+  if (w) *err_host = w;
 }
+__global__ void k_set_next_id(MapCounters* ctr, uint32_t v) { ctr->next_id = v; }
 __global__ void k_reset_batch(MapCounters* ctr) { ctr->batch_alive = 0; }
 
 // ---- Delete_Point_Boxes --------------------------------------------------------------------------
@@ -483,14 +358,23 @@ int map_alloc(lio_ctx* c) {
   // one head bucket per cell plus overflow room for cells holding more than kSlots points
   m.pool_cap = (uint32_t)std::min<uint64_t>(cells + cfg.max_points / kSlots + 1024, 0x7FFFFFFFull);
   LIO_CUDA(cudaMalloc(&m.table, sizeof(HashEntry) * (size_t)c->table_cap));
-  LIO_CUDA(cudaMalloc(&m.slots, sizeof(float4) * kSlots * (size_t)m.pool_cap));
-  LIO_CUDA(cudaMalloc(&m.next, sizeof(uint32_t) * (size_t)m.pool_cap));
+  m.cell_limit = c->table_cap / 2;
+  // + the null bucket (index pool_cap): what a cell created under pool exhaustion points at; always empty
+  LIO_CUDA(cudaMalloc(&m.slots, sizeof(float4) * kSlots * ((size_t)m.pool_cap + 1)));
+  LIO_CUDA(cudaMalloc(&m.next, sizeof(uint32_t) * ((size_t)m.pool_cap + 1)));
   // occupancy words: >= one per 2 cells of capacity (a 4x4x4 block usually holds several cells, so most words stay private)
   const uint64_t occ_words = next_pow2(std::max<uint64_t>(1u << 14, cells / 2));
   m.occ_mask = (uint32_t)(occ_words - 1);
   LIO_CUDA(cudaMalloc(&m.occ, sizeof(unsigned long long) * (size_t)occ_words));
   LIO_CUDA(cudaMalloc(&m.ctr, sizeof(MapCounters)));
   LIO_CUDA(cudaMalloc(&c->boxes_dev, sizeof(float) * 6 * 64));
+  LIO_CUDA(cudaHostAlloc(&c->map_err_host, 64, cudaHostAllocMapped));
+  std::memset(c->map_err_host, 0, 64);
+  LIO_CUDA(cudaHostGetDevicePointer(&c->map_err_dev, c->map_err_host, 0));
+  {
+    const char* e = getenv("LIO_MAP_COMPACT");
+    c->auto_compact = !(e && std::strcmp(e, "0") == 0);
+  }
   LIO_CUDA(cudaMemsetAsync(m.ctr, 0, sizeof(MapCounters), c->stream));
   return map_clear(c);
 }
@@ -503,6 +387,8 @@ void map_free(lio_ctx* c) {
   cudaFree(m.occ);
   cudaFree(m.ctr);
   cudaFree(c->boxes_dev);
+  if (c->map_err_host) cudaFreeHost(c->map_err_host);
+  c->map_err_host = c->map_err_dev = nullptr;
   cudaFree(c->batch_pts);
   cudaFree(c->batch_ent);
   cudaFree(c->batch_tslot);
@@ -517,8 +403,8 @@ void map_free(lio_ctx* c) {
 int map_clear(lio_ctx* c) {
   MapView& m = c->map;
   LIO_CUDA(cudaMemsetAsync(m.table, 0xFF, sizeof(HashEntry) * (size_t)c->table_cap, c->stream));
-  LIO_CUDA(cudaMemsetAsync(m.slots, 0xFF, sizeof(float4) * kSlots * (size_t)m.pool_cap, c->stream));
-  LIO_CUDA(cudaMemsetAsync(m.next, 0xFF, sizeof(uint32_t) * (size_t)m.pool_cap, c->stream));
+  LIO_CUDA(cudaMemsetAsync(m.slots, 0xFF, sizeof(float4) * kSlots * ((size_t)m.pool_cap + 1), c->stream));
+  LIO_CUDA(cudaMemsetAsync(m.next, 0xFF, sizeof(uint32_t) * ((size_t)m.pool_cap + 1), c->stream));
   LIO_CUDA(cudaMemsetAsync(m.occ, 0, sizeof(unsigned long long) * ((size_t)m.occ_mask + 1), c->stream));
   // keep next_id and the sticky error word, zero the rest
   LIO_CUDA(cudaMemsetAsync(&m.ctr->pool_top, 0, sizeof(uint32_t) * 3, c->stream));
@@ -561,7 +447,7 @@ int map_add_device(lio_ctx* c, const float4* pts, uint32_t n_max, const uint32_t
   timer_begin(c, T_INSERT);
   k_cells_ensure<<<grid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent);
   if (!downsample) {
-    k_insert_plain_g<<<ggrid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent);
+    k_insert_plain_g<false><<<ggrid, block, 0, c->stream>>>(m, pts, n_max, n_dev, c->batch_ent);
     c->launches += 2;
   } else {
     // the arbitration table only needs to cover this batch
@@ -575,7 +461,7 @@ int map_add_device(lio_ctx* c, const float4* pts, uint32_t n_max, const uint32_t
                                                   c->batch_ebest, c->batch_ecnt);
     c->launches += 4;
   }
-  k_advance_ids<<<1, 1, 0, c->stream>>>(m.ctr, n_max, n_dev);
+  k_advance_ids<<<1, 1, 0, c->stream>>>(m.ctr, n_max, n_dev, c->map_err_dev);
   c->launches += 1;
   timer_end(c);
   LIO_CUDA(cudaGetLastError());
@@ -593,8 +479,52 @@ int map_delete_boxes(lio_ctx* c, const float* boxes_host, int nb) {
   k_delete_boxes<<<c->n_sms * 8, 256, 0, c->stream>>>(c->map, c->boxes_dev, nb);
   c->launches += 2;
   LIO_CUDA(cudaGetLastError());
-  // the host copy of `boxes_host` may go away once we return
+  // the host copy of `boxes_host` may go away once we return; the counters decide whether the store is worth compacting
+  MapCounters ctr;
+  LIO_CUDA(cudaMemcpyAsync(&ctr, c->map.ctr, sizeof(MapCounters), cudaMemcpyDeviceToHost, c->stream));
   LIO_CUDA(cudaStreamSynchronize(c->stream));
+  c->last_deleted = ctr.deleted;
+  c->dead_since_compact += ctr.deleted;
+  // a sliding local map deletes as much as it inserts: without reclaiming, pool_top / n_cells only grow.  Compact when one of
+  // the pools is three quarters used and a good part of what it holds is dead.
+  const bool crowded = (uint64_t)ctr.pool_top * 4 > (uint64_t)c->map.pool_cap * 3 || (uint64_t)ctr.n_cells * 4 > (uint64_t)c->map.cell_limit * 3;
+  if (c->auto_compact && crowded && c->dead_since_compact * 4 > (uint64_t)std::max(ctr.live, 1)) return map_compact(c, false);
+  return LIO_OK;
+}
+
+// Rebuilds the store from its live points: dead cells, emptied buckets and overflow chains left behind by
+// Delete_Point_Boxes / downsample replacements are reclaimed (table, pool and occupancy words start over).  Ids are kept, so
+// every search and flatten() returns what it returned before; `renumber` replaces them by their rank (same order, same
+// tie-breaks) and restarts the insertion counter at the live count - what keeps the 32-bit id from wrapping on long drives.
+int map_compact(lio_ctx* c, bool renumber) {
+  std::vector<float4> pts;
+  int rc = map_export(c, pts);  // sorted by id
+  if (rc) return rc;
+  rc = map_clear(c);
+  if (rc) return rc;
+  const uint32_t n = (uint32_t)pts.size();
+  if (renumber)
+    for (uint32_t i = 0; i < n; ++i) std::memcpy(&pts[i].w, &i, 4);
+  if (n) {
+    rc = map_ensure_batch(c, n);
+    if (rc) return rc;
+    LIO_CUDA(cudaMemcpyAsync(c->batch_pts, pts.data(), sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    const int block = 256, grid = grid_for(c, n, block);
+    const int ggrid = grid_for(c, (uint32_t)std::min<uint64_t>((uint64_t)n * 8, 0x7FFFFFFFull), block);
+    k_cells_ensure<<<grid, block, 0, c->stream>>>(c->map, c->batch_pts, n, nullptr, c->batch_ent);
+    k_insert_plain_g<true><<<ggrid, block, 0, c->stream>>>(c->map, c->batch_pts, n, nullptr, c->batch_ent);
+    c->launches += 2;
+  }
+  if (renumber) {
+    k_set_next_id<<<1, 1, 0, c->stream>>>(c->map.ctr, n);
+    c->launches += 1;
+  }
+  LIO_CUDA(cudaGetLastError());
+  LIO_CUDA(cudaStreamSynchronize(c->stream));  // `pts` goes away
+  if (renumber) *c->map_err_host &= ~kWarnIdsHigh;
+  c->dead_since_compact = 0;
+  // (cached neighbours of the scan in flight keep their coordinates, which is all map_incremental reads; after a renumbering
+  // the ids lio_scan_get reports for that one scan are the old ones)
   return LIO_OK;
 }
 
@@ -606,6 +536,18 @@ int map_read_counters(lio_ctx* c, MapCounters* out) {
               (out->error & kErrHashFull) ? "hash table " : "", (out->error & kErrPoolFull) ? "bucket pool" : "");
     return LIO_E_CAPACITY;
   }
+  return LIO_OK;
+}
+
+// Called at the top of the hot-path entry points: the mapped word carries what the last insert left behind.
+int map_check_health(lio_ctx* c) {
+  const uint32_t w = *reinterpret_cast<volatile uint32_t*>(c->map_err_host);
+  if (w & (kErrHashFull | kErrPoolFull)) {
+    set_error("map capacity exhausted (%s%s): points were dropped; raise lio_config.max_points / max_cells",
+              (w & kErrHashFull) ? "hash table " : "", (w & kErrPoolFull) ? "bucket pool" : "");
+    return LIO_E_CAPACITY;
+  }
+  if (w & kWarnIdsHigh) return map_compact(c, true);
   return LIO_OK;
 }
 

@@ -220,7 +220,8 @@ __global__ void __launch_bounds__(kSortScanBlock) k_sort_scan(SortScratch* __res
 }
 
 __global__ void __launch_bounds__(256) k_sort_place(const uint32_t* __restrict__ keys, const KeysArgs* __restrict__ a, int n_val,
-                                                    SortScratch* __restrict__ sc, uint32_t* __restrict__ order) {
+                                                    SortScratch* __restrict__ sc, uint32_t* __restrict__ order,
+                                                    const float4* __restrict__ pts, float4* __restrict__ sorted) {
   const int n = a ? a->n : n_val;
   const int lane = threadIdx.x & 31;
   uint32_t* hist2 = sort_hist2(sc);
@@ -238,7 +239,9 @@ __global__ void __launch_bounds__(256) k_sort_place(const uint32_t* __restrict__
       base = sc->start[cube] + atomicAdd(&hist2[(size_t)slot * kSortBins + (key & kSortLowMask)], (uint32_t)__popc(pk));
     }
     base = __shfl_sync(pk, base, leader);
-    order[base + __popc(pk & ((1u << lane) - 1u))] = (uint32_t)i;
+    const uint32_t pos = base + __popc(pk & ((1u << lane) - 1u));
+    order[pos] = (uint32_t)i;
+    sorted[pos] = __ldg(pts + i);  // the search reads its 32 queries with one coalesced load instead of a gather through order[]
   }
 }
 
@@ -274,66 +277,152 @@ __device__ __forceinline__ const StateArg& block_state(const StateArg& st_param,
   return st_param;
 }
 
-// One warp per tile of 32 queries taken in `order` (tiles handed out through an atomic counter); results are scattered
-// back to the queries' own rows.  ctr[0] = tile counter, ctr[1] = leftover count (both zeroed by the previous k_knn_left).
+// Persistent warps draw tasks from the search's work queue (lio_knn_tile.cuh): a tile of 32 curve-ordered queries, or a
+// (tile, lane mask) sub-tile another warp pushed.  `sorted` holds the query points in curve order (written by k_sort_place), so
+// a task reads its 32 queries with one coalesced load; results are scattered back to the queries' own rows through `order`.
+// q = this search's counter set (zeroed by the previous search's k_knn_left).
 template <bool XFORM, bool DEV>
-__global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ order,
+__global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, const float4* __restrict__ sorted, const uint32_t* __restrict__ order,
                                                                int n, StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
-                                                               float* __restrict__ nn_d2, int* __restrict__ nn_cnt,
-                                                               uint32_t* __restrict__ ctr, uint32_t* __restrict__ left,
-                                                               const IekfCtl* __restrict__ ctl, uint32_t* __restrict__ stats,
-                                                               uint4* __restrict__ prof_out) {
+                                                               float* __restrict__ nn_d2, int* __restrict__ nn_cnt, TileQueue* __restrict__ q,
+                                                               unsigned long long* __restrict__ queue, uint32_t qcap,
+                                                               uint32_t* __restrict__ left, const IekfCtl* __restrict__ ctl,
+                                                               uint32_t* __restrict__ stats, uint4* __restrict__ prof_out, uint32_t prof_cap) {
   __shared__ TileSmem smem[kTileWarps];
   __shared__ StateArg s_st;
   if (DEV && (ctl->finished || !ctl->converge)) return;  // cached neighbours are reused (ekfom_data.converge == false)
   const StateArg& st = block_state<DEV>(st_param, ctl, s_st);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned lt = (1u << lane) - 1u;
   TileSmem& sm = smem[warp];
-  const int tiles = (n + 31) / 32;
+  const uint32_t tiles = (uint32_t)((n + 31) / 32);
   const float4 pad = make_float4(0.f, 0.f, 0.f, __uint_as_float(kEmptyId));
   const float inf = __int_as_float(0x7f800000);
-  while (true) {
-    int tile = 0;
-    if (lane == 0) tile = (int)atomicAdd(ctr, 1u);
-    tile = __shfl_sync(0xFFFFFFFFu, tile, 0);
-    if (tile >= tiles) break;
-    const int t = tile * 32 + lane;
-    const bool valid = t < n;
-    const uint32_t i = valid ? __ldg(order + t) : 0u;
+  uint32_t ticket, tile;
+  unsigned mask;
+  while (tile_next_task(q, queue, qcap, tiles, lane, ticket, tile, mask)) {
+    const int t = (int)tile * 32 + lane;
+    const bool valid = t < n && ((mask >> lane) & 1u);
+    uint32_t i = 0u;
     float qx = 0.f, qy = 0.f, qz = 0.f;
     if (valid) {
-      const float4 b = __ldg(pts + i);
+      i = __ldg(order + t);
+      const float4 b = __ldg(sorted + t);
       qx = b.x, qy = b.y, qz = b.z;
       if (XFORM) body_to_world(st, b.x, b.y, b.z, qx, qy, qz);
     }
-    unsigned overflow = 0;
-    TileProf prof{0, 0, 0};
+    TileProf prof{0, 0, 0, 0};
     const long long t0 = prof_out ? clock64() : 0;
-    const unsigned pending = tile_search(m, sm, lane, qx, qy, qz, valid, max_d2, [&](const Top32& L, int cnt) {
+    unsigned long long g0 = 0;
+    if (prof_out) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
+    const int cx = vox_of(qx, m.ds) >> m.cell_shift, cy = vox_of(qy, m.ds) >> m.cell_shift, cz = vox_of(qz, m.ds) >> m.cell_shift;
+    // the sub-tile of the first query stays here; the others are pushed right away, before any memory is touched
+    unsigned pending = __ballot_sync(0xFFFFFFFFu, valid);
+    unsigned sub = 0, to_left = 0;
+    int n_push = 0;
+    unsigned my_push = 0;
+    {
+      unsigned r = pending;
+      while (r) {
+        const int a = __ffs(r) - 1;
+        const int ax0 = __shfl_sync(0xFFFFFFFFu, cx, a), ay0 = __shfl_sync(0xFFFFFFFFu, cy, a), az0 = __shfl_sync(0xFFFFFFFFu, cz, a);
+        const bool near = ((r >> lane) & 1u) && (c_tile_block ? ((cx >> 1) == (ax0 >> 1) && (cy >> 1) == (ay0 >> 1) && (cz >> 1) == (az0 >> 1))
+                                                              : (abs(cx - ax0) <= kTileSpan && abs(cy - ay0) <= kTileSpan && abs(cz - az0) <= kTileSpan));
+        const unsigned s2 = __ballot_sync(0xFFFFFFFFu, near);
+        r &= ~s2;
+        if (!sub) {
+          sub = s2;
+        } else {
+          if (lane == n_push) my_push = s2;
+          ++n_push;
+        }
+      }
+    }
+    // the other sub-tiles are offered on the queue before this warp touches the map: free warps start on them right away
+    uint32_t push_base = 0;
+    bool offered = false;
+    if (ticket < tiles) {
+      if (n_push) {
+        if (lane == 0) push_base = atomicAdd(&q->tail, (uint32_t)n_push);
+        push_base = __shfl_sync(0xFFFFFFFFu, push_base, 0);
+        offered = c_tile_offer && push_base + (uint32_t)n_push <= qcap;  // (always, with qcap = 2 n)
+        if (offered && lane < n_push) atomicExch(queue + push_base + lane, ((unsigned long long)tile << 32) | my_push);
+        __syncwarp();
+      }
+      if (lane == 0) atomicAdd(&q->split_done, 1u);
+    }
+    auto emit = [&](const uint32_t (&rs)[kK], int cnt) {
       cnt = min(cnt, k);
-      const uint32_t ks[kK] = {L.b0, L.b1, L.b2, L.b3, L.b4};
-      const uint32_t rs[kK] = {L.r0, L.r1, L.r2, L.r3, L.r4};
 #pragma unroll
       for (int j = 0; j < kK; ++j)
         if (j < k) {
           const bool have = j < cnt;
-          nn[(size_t)i * k + j] = have ? sm.pts[rs[j]] : pad;
-          if (nn_d2) nn_d2[(size_t)i * k + j] = have ? __uint_as_float(ks[j]) : inf;
+          const float4 c = have ? sm.pts[rs[j]] : pad;
+          nn[(size_t)i * k + j] = c;
+          if (nn_d2) nn_d2[(size_t)i * k + j] = have ? sqdist3(qx, qy, qz, c.x, c.y, c.z) : inf;
         }
       nn_cnt[i] = cnt;
-    }, &overflow, prof_out ? &prof : nullptr);
-    if (prof_out && lane == 0)
-      prof_out[tile] = make_uint4((uint32_t)(clock64() - t0), (uint32_t)prof.passes | ((uint32_t)__popc(pending) << 8) | ((uint32_t)__popc(overflow) << 16),
-                                  (uint32_t)prof.staged, (uint32_t)prof.cells);
-    if (pending) {  // defer to k_knn_left
-      if (lane == 0 && stats) {  // [1] staging overflow / growth limit, [2] tile too incoherent (beyond kTileMaxSub sub-tiles)
-        if (overflow) atomicAdd(stats + 1, (uint32_t)__popc(overflow));
-        if (pending & ~overflow) atomicAdd(stats + 2, (uint32_t)__popc(pending & ~overflow));
+    };
+    // Sets of lanes (coherent sub-tiles) are served one after the other through ONE call site of the search: the own
+    // sub-tile first, then (stage 1) whatever of the offers nobody took, taken back with a compare-and-swap.  When the
+    // candidates of a set overflow the staging area (a dense corner: the box of a sub-tile can reach 5 x 5 x 5 cells) its
+    // lanes are served cell by cell - the queries of one cell stage 27 cells; if even that overflows they go to the per-query kernel.
+    unsigned set = sub, back = 0u, owners = 0u;
+    if (ticket >= tiles) set = pending;  // (an offered mask is coherent by construction: sub == pending; kept for robustness)
+    int stage = 0;
+    bool by_cell = false;
+    while (true) {
+      if (!set) {
+        if (stage == 0) {
+          stage = 1;
+          if (ticket < tiles && n_push) {
+            back = offered ? 0u : my_push;
+            if (offered && lane < n_push) {
+              const unsigned long long val = ((unsigned long long)tile << 32) | my_push;
+              if (atomicCAS(queue + push_base + lane, val, 0ull) == val) back = my_push;
+            }
+            owners = __ballot_sync(0xFFFFFFFFu, lane < n_push && back != 0u);
+          }
+        }
+        if (!owners) break;
+        const int c = __ffs(owners) - 1;
+        owners &= owners - 1;
+        set = __shfl_sync(0xFFFFFFFFu, back, c);
+        by_cell = false;
       }
+      unsigned part = set;
+      if (by_cell) {  // the lanes of the set that share the cell of its first lane
+        const int a = __ffs(set) - 1;
+        const int ax0 = __shfl_sync(0xFFFFFFFFu, cx, a), ay0 = __shfl_sync(0xFFFFFFFFu, cy, a), az0 = __shfl_sync(0xFFFFFFFFu, cz, a);
+        part = __ballot_sync(0xFFFFFFFFu, ((set >> lane) & 1u) && cx == ax0 && cy == ay0 && cz == az0);
+      }
+      const unsigned failed = tile_search_sub(m, sm, lane, qx, qy, qz, cx, cy, cz, part, max_d2, emit, prof_out ? &prof : nullptr);
+      set &= ~(part & ~failed);
+      if (failed) {
+        if (by_cell || !c_tile_halve) {
+          to_left |= failed;
+          set &= ~failed;
+        } else {
+          by_cell = true;
+        }
+      }
+    }
+    if (to_left) {
+      if (lane == 0 && stats) atomicAdd(stats + 1, (uint32_t)__popc(to_left));
       uint32_t base = 0;
-      if (lane == 0) base = atomicAdd(ctr + 1, (uint32_t)__popc(pending));
+      if (lane == 0) base = atomicAdd(&q->left, (uint32_t)__popc(to_left));
       base = __shfl_sync(0xFFFFFFFFu, base, 0);
-      if ((pending >> lane) & 1u) left[base + __popc(pending & ((1u << lane) - 1u))] = i;
+      if ((to_left >> lane) & 1u) left[base + __popc(to_left & lt)] = i;
+    }
+    if (lane == 0 && stats && ticket >= tiles) atomicAdd(stats + 2, (uint32_t)__popc(pending));  // queries served through a pushed task
+    if (prof_out && lane == 0 && ticket < prof_cap) {
+      unsigned long long g1;
+      uint32_t smid;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      prof_out[2 * ticket] = make_uint4((uint32_t)(clock64() - t0), (uint32_t)prof.passes | ((uint32_t)__popc(pending & ~to_left) << 8) | ((uint32_t)n_push << 16) |
+                                        ((ticket >= tiles ? 1u : 0u) << 24), (uint32_t)prof.staged, (uint32_t)prof.cells);
+      prof_out[2 * ticket + 1] = make_uint4((uint32_t)g0, (uint32_t)g1, smid, (uint32_t)prof.stage_cycles);
     }
   }
 }
@@ -343,8 +432,8 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
 template <bool XFORM, bool DEV>
 __global__ void __launch_bounds__(kKnnBlock) k_knn_left8(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
                                                         StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
-                                                        float* __restrict__ nn_d2, int* __restrict__ nn_cnt, uint32_t* __restrict__ ctr,
-                                                        uint32_t* __restrict__ ctr_next, uint32_t* __restrict__ stats,
+                                                        float* __restrict__ nn_d2, int* __restrict__ nn_cnt, TileQueue* __restrict__ ctr,
+                                                        TileQueue* __restrict__ ctr_next, uint32_t* __restrict__ stats,
                                                         const IekfCtl* __restrict__ ctl) {
   __shared__ StateArg s_st;
   const Group<8> g;
@@ -352,9 +441,9 @@ __global__ void __launch_bounds__(kKnnBlock) k_knn_left8(MapView m, const float4
   const int gid = blockIdx.x * groups_per_block + (threadIdx.x / 8);
   const int gstride = gridDim.x * groups_per_block;
   const bool skip = DEV && (ctl->finished || !ctl->converge);  // the tile kernel did not run: ctr is still zero
-  const int n_left = skip ? 0 : (int)ctr[1];
+  const int n_left = skip ? 0 : (int)ctr->left;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    ctr_next[0] = ctr_next[1] = 0u;  // the next search uses the other counter pair
+    *ctr_next = TileQueue{0u, 0u, 0u, 0u};  // the next search uses the other counter set
     if (stats && !skip) atomicAdd(stats, (uint32_t)n_left);
   }
   if (skip) return;
@@ -385,8 +474,8 @@ constexpr int kLeftGridMult = 4;  // blocks per SM of k_knn_left
 template <bool XFORM, bool DEV>
 __global__ void __launch_bounds__(kKnnBlock, 4) k_knn_left(MapView m, const float4* __restrict__ pts, const uint32_t* __restrict__ left,
                                                         StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
-                                                        float* __restrict__ nn_d2, int* __restrict__ nn_cnt, uint32_t* __restrict__ ctr,
-                                                        uint32_t* __restrict__ ctr_next, uint32_t* __restrict__ stats,
+                                                        float* __restrict__ nn_d2, int* __restrict__ nn_cnt, TileQueue* __restrict__ ctr,
+                                                        TileQueue* __restrict__ ctr_next, uint32_t* __restrict__ stats,
                                                         const IekfCtl* __restrict__ ctl) {
   __shared__ StateArg s_st;
   __shared__ WarpList s_wl[kKnnBlock / 32];
@@ -395,9 +484,9 @@ __global__ void __launch_bounds__(kKnnBlock, 4) k_knn_left(MapView m, const floa
   const int wid = blockIdx.x * warps_per_block + warp;
   const int wstride = gridDim.x * warps_per_block;
   const bool skip = DEV && (ctl->finished || !ctl->converge);  // the tile kernel did not run: ctr is still zero
-  const int n_left = skip ? 0 : (int)ctr[1];
+  const int n_left = skip ? 0 : (int)ctr->left;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    ctr_next[0] = ctr_next[1] = 0u;  // the next search uses the other counter pair
+    *ctr_next = TileQueue{0u, 0u, 0u, 0u};  // the next search uses the other counter set
     if (stats && !skip) atomicAdd(stats, (uint32_t)n_left);
   }
   if (skip) return;
@@ -894,8 +983,8 @@ int scan_alloc(lio_ctx* c) {
   LIO_CUDA(cudaMalloc(&c->blk_cnt, sizeof(uint32_t) * 2 * ((n + 255) / 256 + 1)));
   LIO_CUDA(cudaMalloc(&c->list_add, sizeof(float4) * n));
   LIO_CUDA(cudaMalloc(&c->list_nodown, sizeof(float4) * n));
-  LIO_CUDA(cudaMalloc(&c->tile_stats, sizeof(uint32_t) * 8));  // [0..3] stats, [4..7] two (tile, leftover) counter pairs
-  LIO_CUDA(cudaMemsetAsync(c->tile_stats, 0, sizeof(uint32_t) * 8, c->stream));
+  LIO_CUDA(cudaMalloc(&c->tile_stats, sizeof(uint32_t) * 12));  // [0..3] stats, [4..11] the two TileQueue counter sets
+  LIO_CUDA(cudaMemsetAsync(c->tile_stats, 0, sizeof(uint32_t) * 12, c->stream));
   {
     const char* e = getenv("LIO_KNN_MODE");
     c->knn_mode = (e && std::strcmp(e, "group") == 0) ? 0 : 1;
@@ -909,12 +998,27 @@ int scan_alloc(lio_ctx* c) {
       e = getenv("LIO_TILE_ORDER");
       const int hil = (e && (e[0] == 'm' || e[0] == '0')) ? 0 : 1;
       LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_hilbert, &hil, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
+      e = getenv("LIO_TILE_OFFER");
+      const int offer = (e && e[0] == '0') ? 0 : 1;
+      LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_offer, &offer, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
+      e = getenv("LIO_TILE_GROUP");
+      const int blk = (e && e[0] == 'b') ? 1 : 0;
+      LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_block, &blk, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
+      e = getenv("LIO_TILE_HALVE");
+      const int halve = (e && e[0] == '1') ? 1 : 0;
+      LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_halve, &halve, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
       LIO_CUDA(cudaStreamSynchronize(c->stream));
     }
     e = getenv("LIO_TILE_PROF");  // per-tile cycle / pass counters of the last scan search (lio_tile_profile)
-    if (e && std::strcmp(e, "1") == 0) LIO_CUDA(cudaMalloc(&c->tile_prof, sizeof(uint4) * ((n + 31) / 32 + 1)));
+    if (e && std::strcmp(e, "1") == 0) {
+      c->tile_prof_cap = 2 * (uint32_t)((n + 31) / 32 + 1);  // tickets recorded: the tiles and as many pushed tasks
+      LIO_CUDA(cudaMalloc(&c->tile_prof, sizeof(uint4) * 2 * (size_t)c->tile_prof_cap));
+      LIO_CUDA(cudaMemsetAsync(c->tile_prof, 0, sizeof(uint4) * 2 * (size_t)c->tile_prof_cap, c->stream));
+    }
     e = getenv("LIO_BATCH_LEFT");
     c->batch_left_warp = (e && std::strcmp(e, "warp") == 0) ? 1 : 0;
+    e = getenv("LIO_RESORT");
+    c->resort_each_search = !(e && e[0] == '0');
     e = getenv("LIO_SORT_GRAPH");
     c->sort_graph_ok = !(e && std::strcmp(e, "0") == 0);
     e = getenv("LIO_MAP_GRAPH");
@@ -958,6 +1062,8 @@ void scan_free(lio_ctx* c) {
     cudaFree(c->tile_keys[j]);
     cudaFree(c->tile_vals[j]);
   }
+  cudaFree(c->tile_sorted);
+  cudaFree(c->tile_queue);
   if (c->out_host) cudaFreeHost(c->out_host);
   for (auto& g : c->sort_graphs) cudaGraphExecDestroy((cudaGraphExec_t)g.second);
   c->sort_graphs.clear();
@@ -1005,10 +1111,17 @@ int tile_ensure(lio_ctx* c, uint32_t n) {
     cudaFree(c->tile_vals[j]);
     c->tile_keys[j] = c->tile_vals[j] = nullptr;
   }
+  cudaFree(c->tile_sorted);
+  cudaFree(c->tile_queue);
+  c->tile_sorted = nullptr;
+  c->tile_queue = nullptr;
   c->tile_cap = 0;
   const uint32_t cap = n + n / 8 + 1024;
   LIO_CUDA(cudaMalloc(&c->tile_keys[0], sizeof(uint32_t) * cap));  // keys
   for (int j = 0; j < 2; ++j) LIO_CUDA(cudaMalloc(&c->tile_vals[j], sizeof(uint32_t) * cap));  // [0] leftover list, [1] order
+  LIO_CUDA(cudaMalloc(&c->tile_sorted, sizeof(float4) * cap));                                  // the query points in curve order
+  LIO_CUDA(cudaMalloc(&c->tile_queue, sizeof(unsigned long long) * 2 * (size_t)cap));           // pushed (tile, lane mask) tasks
+  LIO_CUDA(cudaMemsetAsync(c->tile_queue, 0, sizeof(unsigned long long) * 2 * (size_t)cap, c->stream));  // self-cleaning afterwards
   c->tile_cap = cap;
   c->order_valid = false;
   return LIO_OK;
@@ -1024,7 +1137,7 @@ static void sort_launch(lio_ctx* c, const float4* pts, int n_grid, const KeysArg
   else
     k_sort_count<false><<<grid, 256, 0, c->stream>>>(c->map, pts, args, st, n, c->tile_keys[0], sc);
   k_sort_scan<<<1 + c->n_sms * 3, kSortScanBlock, 0, c->stream>>>(sc);  // block 0: level 1; the others stride over the slots in use
-  k_sort_place<<<grid, 256, 0, c->stream>>>(c->tile_keys[0], args, n, sc, c->tile_vals[1]);
+  k_sort_place<<<grid, 256, 0, c->stream>>>(c->tile_keys[0], args, n, sc, c->tile_vals[1], pts, c->tile_sorted);
   k_sort_clear<<<c->n_sms * 2, 256, 0, c->stream>>>(sc);
   c->launches += 4;
 }
@@ -1083,15 +1196,27 @@ static int tile_order_graph(lio_ctx* c, int n, const double* state_host) {
   return LIO_OK;
 }
 
+// a quarter more warps than tiles (up to 8 blocks per SM): the spare ones start on pushed sub-tiles right away
 static int tile_grid(const lio_ctx* c, int n) {
   const int tiles = (n + 31) / 32;
-  return std::max(1, std::min((tiles + kTileWarps - 1) / kTileWarps, c->n_sms * 8));
+  const int blocks = (tiles + kTileWarps - 1) / kTileWarps;
+  return std::max(1, std::min(blocks + blocks / 4 + 1, c->n_sms * 8));
+}
+
+// tasks (tiles + pushed sub-tiles) of the last search; its counter set stays intact until the next search has run
+int tile_tasks_of_last_search(lio_ctx* c, uint32_t* n_tasks) {
+  TileQueue q;
+  const TileQueue* sets = reinterpret_cast<const TileQueue*>(c->tile_stats + 4);
+  LIO_CUDA(cudaMemcpyAsync(&q, sets + ((c->tile_flip + 1) & 1), sizeof(TileQueue), cudaMemcpyDeviceToHost, c->stream));
+  LIO_CUDA(cudaStreamSynchronize(c->stream));
+  *n_tasks = (uint32_t)((c->scan_n + 31) / 32) + q.tail;
+  return LIO_OK;
 }
 
 int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
   const int n = c->scan_n;
   const StateArg st = make_state(state_host);
-  if (c->knn_mode == 1 && !c->order_valid) {  // once per scan: later calls move the points by centimetres, the order stays coherent
+  if (c->knn_mode == 1 && (!c->order_valid || c->resort_each_search)) {  // LIO_RESORT=0: once per scan (later calls move the points by centimetres)
     timer_begin(c, T_SORT);
     int rc = c->sort_graph_ok ? tile_order_graph(c, n, state_host) : LIO_E_STATE;
     if (rc == LIO_E_STATE && !c->sort_graph_ok) rc = tile_order(c, c->body, n, st, true);
@@ -1101,19 +1226,24 @@ int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
   }
   timer_begin(c, T_KNN);
   if (c->knn_mode == 1) {
-    uint32_t* ctr = c->tile_stats + 4 + 2 * (c->tile_flip & 1);
-    uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
+    TileQueue* sets = reinterpret_cast<TileQueue*>(c->tile_stats + 4);
+    TileQueue* ctr = sets + (c->tile_flip & 1);
+    TileQueue* ctr_next = sets + ((c->tile_flip + 1) & 1);
     c->tile_flip ^= 1;
+    const uint32_t qcap = 2 * c->tile_cap;
+    // nn_d2 is not written on the scan path: nothing downstream reads it (the plane fit and map_incremental use the points)
     if (dev_loop) {
-      k_knn_tile<true, true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
-                                                                                  c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], c->iekf_ctl, c->tile_stats, c->tile_prof);
+      k_knn_tile<true, true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->tile_sorted, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
+                                                                                  c->nn, nullptr, c->nn_cnt, ctr, c->tile_queue, qcap, c->tile_vals[0],
+                                                                                  c->iekf_ctl, c->tile_stats, c->tile_prof, c->tile_prof_cap);
       k_knn_left<true, true><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
-                                                                         c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, c->iekf_ctl);
+                                                                         nullptr, c->nn_cnt, ctr, ctr_next, c->tile_stats, c->iekf_ctl);
     } else {
-      k_knn_tile<true, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->body, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
-                                                                                   c->nn, c->nn_d2, c->nn_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats, c->tile_prof);
+      k_knn_tile<true, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->tile_sorted, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
+                                                                                   c->nn, nullptr, c->nn_cnt, ctr, c->tile_queue, qcap, c->tile_vals[0],
+                                                                                   nullptr, c->tile_stats, c->tile_prof, c->tile_prof_cap);
       k_knn_left<true, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
-                                                                          c->nn_d2, c->nn_cnt, ctr, ctr_next, c->tile_stats, nullptr);
+                                                                          nullptr, c->nn_cnt, ctr, ctr_next, c->tile_stats, nullptr);
     }
     c->launches += 1;
   } else {
@@ -1135,11 +1265,13 @@ int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float
     if (rc) return rc;
     (void)keep;
     c->order_valid = false;
-    uint32_t* ctr = c->tile_stats + 4 + 2 * (c->tile_flip & 1);
-    uint32_t* ctr_next = c->tile_stats + 4 + 2 * ((c->tile_flip + 1) & 1);
+    TileQueue* sets = reinterpret_cast<TileQueue*>(c->tile_stats + 4);
+    TileQueue* ctr = sets + (c->tile_flip & 1);
+    TileQueue* ctr_next = sets + ((c->tile_flip + 1) & 1);
     c->tile_flip ^= 1;
-    k_knn_tile<false, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, q_dev, c->tile_vals[1], n, st, k, max_d2, out_nn,
-                                                                                  out_d2, out_cnt, ctr, c->tile_vals[0], nullptr, c->tile_stats, nullptr);
+    k_knn_tile<false, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->tile_sorted, c->tile_vals[1], n, st, k, max_d2, out_nn,
+                                                                                  out_d2, out_cnt, ctr, c->tile_queue, 2 * c->tile_cap, c->tile_vals[0],
+                                                                                  nullptr, c->tile_stats, nullptr, 0u);
     if (c->batch_left_warp)
       k_knn_left<false, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
                                                                          ctr, ctr_next, c->tile_stats, nullptr);

@@ -66,6 +66,16 @@ int lio_map_add(lio_ctx* ctx, const float* xyz, int n, int downsample_on, int* n
 /* Delete_Point_Boxes: nb boxes of 6 floats (min xyz, max xyz), half-open.  *n_deleted optional. */
 int lio_map_delete_boxes(lio_ctx* ctx, const float* boxes, int nb, int* n_deleted);
 int lio_map_size(lio_ctx* ctx, int* n_live);
+/* Rebuilds the store from its live points (ikd-Tree reclaims deleted nodes when it rebuilds a sub-tree; here cells, buckets
+ * and overflow chains emptied by Delete_Point_Boxes are handed back in one pass).  Ids are kept, so every search and
+ * lio_map_export returns exactly what it returned before; renumber_ids != 0 replaces them by their rank (same order and
+ * tie-breaks) and restarts the insertion counter at the live count.  Runs by itself after a box delete once a pool is three
+ * quarters used and a quarter of the live count has been deleted since the last compaction (LIO_MAP_COMPACT=0 disables
+ * that), and with renumbering when the 32-bit insertion counter passes 0xC0000000. */
+int lio_map_compact(lio_ctx* ctx, int renumber_ids);
+/* out8: live points, insertion counter, buckets handed out, bucket capacity, cells in the table, cell limit, sticky error
+ * bits (1 hash table full, 2 bucket pool full), points deleted since the last compaction. */
+int lio_map_stats(lio_ctx* ctx, uint64_t* out8);
 /* flatten(): live points in ascending id; returns total live count in *n_total, copies min(cap, total). */
 int lio_map_export(lio_ctx* ctx, float* xyz, uint32_t* ids, int cap, int* n_total);
 /* Nearest_Search, batched: n queries (host xyz) -> k<=5 neighbours each within max_sqdist, ascending
@@ -143,13 +153,16 @@ int lio_timing_get(lio_ctx* ctx, const char* name, double* mean_ms, int* launche
 int lio_timing_reset(lio_ctx* ctx);
 /* queries of all searches so far that left the shared-memory tile path for the per-query fallback search */
 int lio_knn_stats(lio_ctx* ctx, uint64_t* fallback_queries);
-/* out4: [0] queries finished by the per-query kernel, [1] of those deferred because a tile's staging area or growth limit
- * overflowed, [2] deferred because the tile was too incoherent, [3] reserved.  Running totals since context creation. */
+/* out4: [0] queries finished by the per-query kernel, [1] queries handed to it because a single query overflowed the
+ * staging area, [2] queries served through a pushed sub-tile task (their tile was not coherent), [3] reserved.  Running
+ * totals since context creation. */
 int lio_knn_stats_detail(lio_ctx* ctx, uint64_t* out4);
-/* Per-tile counters of the last scan search (context created with LIO_TILE_PROF=1 in the environment): 4 words per tile of
- * 32 curve-ordered queries = {SM cycles, staging passes | deferred queries << 8 | overflowed << 16, staged points, cells
- * probed}.  Copies min(cap_tiles, tiles) records; *n_tiles = tiles of the current scan. */
-int lio_tile_profile(lio_ctx* ctx, uint32_t* out4, int cap_tiles, int* n_tiles);
+/* Per-task counters of the last scan search (context created with LIO_TILE_PROF=1 in the environment).  A task is a tile of
+ * 32 curve-ordered queries or a (tile, lane mask) sub-tile pushed to the search's work queue; records are in ticket order,
+ * the tiles first.  8 words per task = {SM cycles, staging passes | queries served << 8 | tasks pushed << 16 | pushed task
+ * << 24, staged points, cells probed, start ns (low 32 bits of %globaltimer), end ns, SM id, SM cycles spent staging}.
+ * Copies min(cap_tiles, tasks) records; *n_tiles = tasks of the last search. */
+int lio_tile_profile(lio_ctx* ctx, uint32_t* out8, int cap_tiles, int* n_tiles);
 /* Achievable random-gather bandwidth of the device: random 16-byte loads from a table of `table_bytes` (use >= 320 MB so
  * it exceeds L2).  *gbps_16B counts the 16 requested bytes per load, *gbps_sector the 32-byte sectors they drag. */
 int lio_gather_probe(lio_ctx* ctx, uint64_t table_bytes, int reps, double* gbps_16B, double* gbps_sector);

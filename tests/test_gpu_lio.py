@@ -399,6 +399,95 @@ def test_map_delete_boxes_parity(pkg, orc):
     g.close()
 
 
+def test_map_compact_keeps_every_answer(pkg, orc):
+    """lio_map_compact: cells / buckets emptied by box deletes are handed back, every search and the flattened map stay
+    bit-identical (ids kept); with renumbering the ids become ranks and the neighbours' coordinates stay the same."""
+    rng = np.random.default_rng(12)
+    g = pkg.LioContext(0.5, max_points=1 << 16, max_scan=1024)
+    o = orc.OracleLio(0.5)
+    base = rng.uniform(-8, 8, (20000, 3)).astype(np.float32)
+    g.map_build(base)
+    o.map_build(base)
+    boxes = np.array([[-8, -8, -8, 0, 8, 8]], np.float32)  # half of the volume goes
+    assert g.map_delete_boxes(boxes) == o.map_delete_boxes(boxes) > 0
+    q = rng.uniform(-8, 8, (3000, 3)).astype(np.float32)
+    before, st0 = g.map_knn(q, 5, 5.0), g.map_stats()
+    g.map_compact()
+    st1 = g.map_stats()
+    assert st1["live"] == st0["live"] == o.map_size() and st1["next_id"] == st0["next_id"]
+    assert st1["n_cells"] < st0["n_cells"] and st1["pool_top"] < st0["pool_top"] and st1["dead_since_compact"] == 0
+    after, ref = g.map_knn(q, 5, 5.0), o.map_knn(q, 5, 5.0)
+    for a, b, c in zip(before, after, ref):
+        assert np.array_equal(a, b) and np.array_equal(b, c)
+    gx, gi = g.map_export()
+    ox, oi = o.map_export()
+    assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
+    # inserts after the compaction continue the id sequence exactly as the oracle's
+    more = rng.uniform(-3, 3, (3000, 3)).astype(np.float32)
+    assert g.map_add(more, True) == o.map_add(more, True)[0]
+    gx, gi = g.map_export()
+    ox, oi = o.map_export()
+    assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
+    # renumbering: ids -> ranks, coordinates and order unchanged, the insertion counter restarts at the live count
+    g.map_compact(renumber=True)
+    gx2, gi2 = g.map_export()
+    assert np.array_equal(gx2, gx) and np.array_equal(gi2, np.arange(len(gi), dtype=np.uint32)) and g.map_stats()["next_id"] == len(gi)
+    a, b = g.map_knn(q, 5, 5.0), o.map_knn(q, 5, 5.0)
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])  # distances and points
+    rank = {int(v): k for k, v in enumerate(oi)}
+    assert np.array_equal(a[0], np.vectorize(lambda v: rank.get(int(v), 0xFFFFFFFF), otypes=[np.uint32])(b[0]))
+    g.close()
+
+
+def test_sliding_map_reclaims_space(pkg, orc):
+    """A local map that slides (insert ahead, box-delete behind) for far more points than the pools hold: the automatic
+    compaction after a delete keeps it running, and the live set stays the oracle's."""
+    rng = np.random.default_rng(13)
+    g = pkg.LioContext(0.5, max_points=24000, max_cells=8000, max_scan=1024)
+    o = orc.OracleLio(0.5)
+    total = 0
+    for step in range(40):
+        x0 = 4.0 * step
+        slab = (rng.uniform(0, 1, (6000, 3)) * [4.0, 12.0, 6.0] + [x0, -6.0, -3.0]).astype(np.float32)
+        assert g.map_add(slab, True) == o.map_add(slab, True)[0]
+        total += len(slab)
+        if step >= 2:
+            box = np.array([[-1e4, -1e4, -1e4, x0 - 8.0, 1e4, 1e4]], np.float32)
+            assert g.map_delete_boxes(box) == o.map_delete_boxes(box)
+    st = g.map_stats()
+    assert st["error"] == 0 and total > 5 * st["pool_cap"] and st["pool_top"] <= st["pool_cap"] and st["n_cells"] <= st["cell_limit"]
+    gx, gi = g.map_export()
+    ox, oi = o.map_export()
+    assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
+    q = (rng.uniform(0, 1, (2000, 3)) * [12.0, 12.0, 6.0] + [4.0 * 37, -6.0, -3.0]).astype(np.float32)
+    a, b = g.map_knn(q, 5, 5.0), o.map_knn(q, 5, 5.0)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    g.close()
+
+
+def test_map_capacity_error_is_loud_and_harmless(pkg, synth, monkeypatch):
+    """Pool / table exhaustion: the add reports LIO_E_CAPACITY, no cell ever aliases another cell's bucket, searches keep
+    running on what was stored, and the hot path (lio_iekf_update_map) refuses to go on silently."""
+    monkeypatch.setenv("LIO_MAP_COMPACT", "0")
+    rng = np.random.default_rng(14)
+    g = pkg.LioContext(0.5, max_points=2048, max_cells=512, max_scan=4096)
+    pts = rng.uniform(-40, 40, (30000, 3)).astype(np.float32)  # ~30 k distinct cells against a limit of a few hundred
+    with pytest.raises(pkg.LioError, match="capacity"):
+        g.map_add(pts, False)
+    st = g.map_stats()
+    assert st["error"] != 0 and st["n_cells"] <= st["cell_limit"] and st["live"] <= len(pts)
+    # every stored point is still found as its own nearest neighbour (nothing was overwritten through an aliased bucket)
+    ids, d2, nn, cnt = g.map_knn(pts[:4000], 1, 1e-12)
+    found = cnt == 1
+    assert found.sum() > 0 and np.array_equal(nn.reshape(-1, 3)[found], pts[:4000][found])
+    scan = rng.uniform(-5, 5, (2000, 3)).astype(np.float32)
+    g.scan_upload(scan)
+    st0 = synth.make_state(np.eye(3), np.zeros(3))
+    with pytest.raises(pkg.LioError, match="capacity"):
+        g.iekf_update_map(st0, synth.default_cov(), True)
+    g.close()
+
+
 def _predict(state, dR, dt):
     """state (+) body-frame motion (dR, dt): pos += rot*dt, rot = rot*dR  (state layout of include/lio_b200.h)."""
     s = state.copy()
