@@ -64,66 +64,73 @@ LEAF, SCORE_THR, RADIUS = 0.3, 1.5, 35.0  # config.yaml:15,12,8 (effective value
 ICP_ALGO_BYTES = 32  # per source point per correspondence pass: 16 B source + 16 B matched target
 
 
-def gpu_loop(loop_mod, w, pairs, device=0, steps=5, warmup=1, stream=None, e2e_steps=3):
-    """loop_verify_batch on this rank's slice.  Returns (results of the last step, mean ms/step from CUDA events on the
-    context's stream, per-kernel-family times, stats, launches per step).  The keyframe store is resident (uploaded once,
-    like keyframes_ in the reference); the timed region is the whole C-ABI call: submap build + VoxelGrid + ICP + D2H."""
+def gpu_loop(loop_mod, w, pairs, device=0, steps=5, warmup=1, stream=None, e2e_steps=3, n_ctx=2):
+    """loop_verify_batch on this rank's slice, through `n_ctx` contexts driven concurrently (loop.LoopClosurePool: the slice is
+    cut into n_ctx contiguous parts).  Returns (results of the last step, mean ms/step, per-kernel-family times, stats, launches
+    per step, e2e).  The keyframe store is resident (uploaded once, like keyframes_ in the reference); the timed region is the
+    whole C-ABI call of every part: submap build + VoxelGrid + ICP + result D2H, HOST WALL CLOCK from a synchronised device
+    to the return of the last part (each call ends with its stream synchronised)."""
     import torch
 
-    g = loop_mod.LoopClosure(num_submap_keyframes=w["range"], voxel_res=LEAF, loop_detection_radius=RADIUS, icp_score_threshold=SCORE_THR,
-                             device=device, stream=stream.cuda_stream if stream is not None else None)
+    kw = dict(num_submap_keyframes=w["range"], voxel_res=LEAF, loop_detection_radius=RADIUS, icp_score_threshold=SCORE_THR, device=device)
+    pool = loop_mod.LoopClosurePool(n_ctx, **kw)
     for c, e, s in zip(w["clouds"], w["est"], w["stamps"]):
-        g.add_keyframe(c, e, s)
+        pool.add_keyframe(c, e, s)
     n = len(pairs)
+    arrays = pool.make_arrays(pairs)
+    for _ in range(warmup):
+        pool.verify_arrays(arrays)
+    l0 = sum(c.launch_count() for c in pool.ctx)
+    times = []
+    for _ in range(steps):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        pool.verify_arrays(arrays)
+        times.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(times) / max(steps, 1)
+    launches = (sum(c.launch_count() for c in pool.ctx) - l0) / max(steps, 1)
+    out = [loop_mod._result(res[i]) for arr, k, res in arrays for i in range(k)]
+    # one extra pass through ONE context over the whole slice with per-kernel CUDA events (they serialise the launches): the
+    # kernel-family breakdown and the batch statistics
+    g = pool.ctx[0]
     arr = (loop_mod.LoopPair * max(n, 1))()
     for i, (a, b) in enumerate(pairs):
         arr[i].src_idx, arr[i].dst_idx = int(a), int(b)
     res = (loop_mod.LoopResult * max(n, 1))()
-    st = stream if stream is not None else torch.cuda.current_stream()
-    for _ in range(warmup):
-        g.verify_batch_raw(arr, n, res)
-    l0 = g.launch_count()
-    evs = []
-    for _ in range(steps):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(st)
-        g.verify_batch_raw(arr, n, res)
-        b.record(st)
-        evs.append((a, b))
-    torch.cuda.synchronize()
-    ms = sum(a.elapsed_time(b) for a, b in evs) / max(steps, 1)
-    launches = (g.launch_count() - l0) / max(steps, 1)
-    g.timing(True)  # one extra, untimed-by-the-bench pass with per-kernel CUDA events (they serialise the launches)
+    g.verify_batch_raw(arr, n, res)  # (untimed: this context has only seen its part so far, its workspace grows here)
+    g.timing(True)
     g.timing_reset()
     g.verify_batch_raw(arr, n, res)
     kt = {k: g.timing_get(k) for k in ("submap", "voxel", "tree", "nn", "cov", "solve", "score")}
     stats = g.batch_stats()
-    out = [loop_mod._result(res[i]) for i in range(n)]
     g.timing(False)
-    # end to end from HOST keyframe clouds: empty store -> loop_keyframe_add of every keyframe (H2D of the clouds) ->
-    # loop_verify_batch -> results back in host memory; host wall clock with a device synchronise on both sides
+    same_split = all(loop_mod._result(res[i])["score"] == out[i]["score"] and np.array_equal(loop_mod._result(res[i])["T"], out[i]["T"]) for i in range(n))
+    # end to end from HOST keyframe clouds: empty stores -> loop_keyframe_add of every keyframe (H2D of the clouds, once per
+    # context) -> loop_verify_batch -> results back in host memory; host wall clock with a device synchronise on both sides
     clouds = [np.ascontiguousarray(c, np.float32) for c in w["clouds"]]
     e2e_s = []
     for _ in range(e2e_steps):
-        g.clear()
+        pool.clear()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for c, e, s in zip(clouds, w["est"], w["stamps"]):
-            g.add_keyframe(c, e, s)
-        g.verify_batch_raw(arr, n, res)
+            pool.add_keyframe(c, e, s)
+        pool.verify_arrays(arrays)
         torch.cuda.synchronize()
         e2e_s.append(time.perf_counter() - t0)
     e2e = None
     if e2e_s:
-        same = all(loop_mod._result(res[i])["score"] == out[i]["score"] and np.array_equal(loop_mod._result(res[i])["T"], out[i]["T"]) for i in range(n))
-        e2e = {"seconds_per_batch": float(np.mean(e2e_s)), "h2d_bytes_per_step": int(sum(c.nbytes for c in clouds) + 17 * 8 * len(clouds) + 8 * n),
-               "d2h_bytes_per_step": int(C.sizeof(loop_mod.LoopResult) * n), "same_results_as_resident_store": bool(same), "batches": len(e2e_s)}
-    g.close()
+        again = [loop_mod._result(r[i]) for a, k, r in arrays for i in range(k)]
+        same = all(x["score"] == y["score"] and np.array_equal(x["T"], y["T"]) for x, y in zip(again, out))
+        e2e = {"seconds_per_batch": float(np.mean(e2e_s)), "h2d_bytes_per_step": int(len(pool.ctx) * (sum(c.nbytes for c in clouds) + 17 * 8 * len(clouds)) + 8 * n),
+               "d2h_bytes_per_step": int(C.sizeof(loop_mod.LoopResult) * n), "same_results_as_resident_store": bool(same), "batches": len(e2e_s),
+               "contexts": len(pool.ctx), "same_results_as_one_context": bool(same_split)}
+    pool.close()
     return out, ms, kt, stats, launches, e2e
 
 
 def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmup, submap_range=12, n_pass=100, n_az=1800,
-                 cpu_pairs=0, stream=None):
+                 cpu_pairs=0, stream=None, n_ctx=None):
     """Runs config 4 on `world` ranks (pairs sharded, no data-path collective) and returns the dict rank 0 reports."""
     import torch
     import torch.distributed as dist
@@ -134,7 +141,8 @@ def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmu
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    res, ms, kt, stats, launches, e2e = gpu_loop(loop_mod, w, mine, device=local_rank, steps=steps, warmup=warmup, stream=stream)
+    n_ctx = int(os.environ.get("LOOP_CONTEXTS", 2)) if n_ctx is None else n_ctx
+    res, ms, kt, stats, launches, e2e = gpu_loop(loop_mod, w, mine, device=local_rank, steps=steps, warmup=warmup, stream=stream, n_ctx=n_ctx)
     t = torch.tensor([ms, 1e3 * e2e["seconds_per_batch"] if e2e else 0.0], dtype=torch.float64, device="cuda")
     gathered = [res]
     per_rank = [(ms, stats["iterations"] / max(len(res), 1))]
@@ -168,6 +176,8 @@ def loop_section(synth, loop_mod, rank, local_rank, world, n_pairs, steps, warmu
         "points_per_keyframe": int(np.mean([len(c) for c in w["clouds"]])), "voxel_res": LEAF, "max_corr_dist": RADIUS * 1.5,
         "results_gathered": len(flat), "valid_total": int(sum(bool(x[1]) for x in flat)) if world > 1 else int(sum(bool(r["valid"]) for r in res)),
         "sharding": "2 contiguous blocks per rank, dealt there and back (loop.shard_pair_indices)",
+        "contexts_per_rank": n_ctx, "timing": "host wall clock around the concurrent loop_verify_batch calls of a rank's contexts, device "
+                                             "synchronised before, max over ranks",
         "per_rank_ms": [round(float(a), 3) for a, _ in per_rank], "per_rank_mean_iterations": [round(float(b), 3) for _, b in per_rank],
         "rank0": {"valid": int(sum(bool(r["valid"]) for r in res)), "converged": int(sum(bool(r["converged"]) for r in res)),
                   "mean_iterations": stats["iterations"] / max(len(res), 1), "mean_src_points": stats["src_points"] / max(len(res), 1),

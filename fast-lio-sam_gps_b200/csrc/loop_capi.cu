@@ -105,6 +105,8 @@ int loop_ctx_create(const loop_config* cfg, loop_ctx** out) {
   c->cfg = *cfg;
   c->n_sms = prop.multiProcessorCount;
   if (const char* e = getenv("LOOP_TREE_ORDER")) c->tree_order = (e[0] == 'm' || e[0] == '0') ? 0 : 1;
+  if (const char* e = getenv("LOOP_GRID")) c->use_grid = e[0] != '0';
+  if (const char* e = getenv("LOOP_SAMPLE_FIRST")) c->sample_first = e[0] != '0';
   c->prm.max_d2 = cfg->max_corr_dist * cfg->max_corr_dist;
   c->prm.trans_eps = cfg->transformation_epsilon;
   c->prm.fit_eps = cfg->euclidean_fitness_epsilon;
@@ -337,6 +339,7 @@ int loop_verify_batch(loop_ctx* c, const loop_pair* pairs, int n_pairs, int rang
       ph.push_back(PairHost{ids[0], ids[1]});
     }
     if ((rc = voxelize_jobs(c, jobs, leaf))) return rc;
+    c->grid_cell = leaf;  // the targets are VoxelGrid outputs at this leaf: about one point per grid cell
     if ((rc = run_icp(c, ph, score_thr, out + done))) return rc;
     it_sum += c->st_iters;
     src_sum += c->st_src;

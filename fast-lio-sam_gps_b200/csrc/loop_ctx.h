@@ -100,6 +100,15 @@ struct TreeDev {
   uint32_t nleaf_pad; // power of two >= nleaf
   uint32_t node_off;  // first node (pairs of child boxes) in the node buffer; nleaf_pad entries, node 0 unused
   uint32_t src_off;   // the cloud's points in the voxelised buffer (original order)
+  // uniform grid over the cloud (targets only): open-addressing table of (cell key -> first point of the cell), points of a
+  // cell chained through gnext[] (indexed like the compact point space).  grid_mask == 0: no grid (the tree alone is used).
+  uint32_t grid_off, grid_mask, cmp_off, pad_;
+};
+
+struct __align__(16) GCell {
+  unsigned long long key;  // packed cell coordinates, ~0: empty
+  uint32_t head;           // original index of the first point of the cell
+  uint32_t pad;
 };
 
 struct __align__(16) Node2 {  // boxes of the two children of a node
@@ -151,6 +160,11 @@ struct loop_ctx {
   loopb::DevBuf<loopb::TreeDev> trees;
   loopb::DevBuf<float4> tree_pts;
   loopb::DevBuf<loopb::Node2> nodes;
+  loopb::DevBuf<loopb::GCell> gtab;   // grids of the target clouds
+  loopb::DevBuf<uint32_t> gnext;      // next point of the same cell (original index inside the cloud), 0xFFFFFFFF: end
+  float grid_cell = 0.3f;             // cell edge of the target grids (the VoxelGrid leaf when the clouds come from it)
+  int use_grid = 0;                   // LOOP_GRID=1: seeded searches probe the target grid first (measured no faster than the seeded tree walk: off)
+  int sample_first = 1;               // LOOP_SAMPLE_FIRST=0: the first iteration searches every point cold (A/B)
   loopb::DevBuf<loopb::PairDev> pairs;
   loopb::DevBuf<float4> cur;
   loopb::DevBuf<int> match;

@@ -183,6 +183,92 @@ __global__ void __launch_bounds__(1024) k_tree_nodes(const TreeDev* __restrict__
   }
 }
 
+// ------------------------------------------------------------------------------------------------ target grid
+// A VoxelGrid output holds about one point per leaf-sized cell, and from the second ICP iteration on a query's previous
+// correspondence lies within millimetres of the new one: every target point that could beat it sits in the one to eight
+// cells the ball around the query touches.  Those are looked up directly (hash of the cell coordinates, points of a cell
+// chained) instead of walking the tree: ~5 dependent loads against ~50 node visits + 8 leaf lines.  The result is the same
+// minimum of (distance, index) over the whole target: every point with d2 <= the seed's distance lies in a probed cell.
+__device__ __forceinline__ unsigned long long gkey(int x, int y, int z) {
+  const unsigned long long m = 0x1FFFFFull;
+  return (((unsigned long long)(x + (1 << 20)) & m) << 42) | (((unsigned long long)(y + (1 << 20)) & m) << 21) | ((unsigned long long)(z + (1 << 20)) & m);
+}
+__device__ __forceinline__ uint32_t ghash(unsigned long long k) {
+  k ^= k >> 33;
+  k *= 0xff51afd7ed558ccdull;
+  k ^= k >> 33;
+  k *= 0xc4ceb9fe1a85ec53ull;
+  k ^= k >> 33;
+  return (uint32_t)k;
+}
+__device__ __forceinline__ int gcell_of(float v, float inv) { return (int)floorf(v * inv); }
+
+__global__ void __launch_bounds__(kBlock) k_tree_grid(const TreeDev* __restrict__ trees, const uint32_t* __restrict__ cmp_off, int n_trees,
+                                                      uint32_t n_total, const float4* __restrict__ vox, GCell* __restrict__ gtab,
+                                                      uint32_t* __restrict__ gnext, float inv) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_total) return;
+  const int t = find_tree(cmp_off, n_trees, i);
+  const TreeDev tr = trees[t];
+  if (!tr.grid_mask) return;
+  const uint32_t l = i - cmp_off[t];
+  const float4 p = __ldg(vox + tr.src_off + l);
+  gnext[i] = 0xFFFFFFFFu;
+  if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) return;
+  const unsigned long long key = gkey(gcell_of(p.x, inv), gcell_of(p.y, inv), gcell_of(p.z, inv));
+  GCell* tab = gtab + tr.grid_off;
+  uint32_t s = ghash(key) & tr.grid_mask;
+  while (true) {
+    unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&tab[s].key);
+    if (cur == ~0ull) cur = atomicCAS(&tab[s].key, ~0ull, key);
+    if (cur == ~0ull || cur == key) break;
+    s = (s + 1) & tr.grid_mask;  // (the table is at least twice the point count: an empty entry always exists)
+  }
+  gnext[i] = atomicExch(&tab[s].head, l);
+}
+
+__device__ __constant__ int c_grid_max_cells = 8;  // LOOP_GRID_MAXC
+// Seeded exact 1-NN through the grid.  Returns false when the ball touches more than c_grid_max_cells cells (the caller walks the tree).
+__device__ __forceinline__ bool grid_probe(const TreeDev& tr, const GCell* __restrict__ gtab, const uint32_t* __restrict__ gnext,
+                                           const float4* __restrict__ target, float inv, float qx, float qy, float qz, float& bd,
+                                           uint32_t& bi, float4& bp) {
+  const float r = sqrtf(bd) * 1.0001f + 1e-6f;
+  const int x0 = gcell_of(qx - r, inv), x1 = gcell_of(qx + r, inv);
+  const int y0 = gcell_of(qy - r, inv), y1 = gcell_of(qy + r, inv);
+  const int z0 = gcell_of(qz - r, inv), z1 = gcell_of(qz + r, inv);
+  const long long nc = (long long)(x1 - x0 + 1) * (y1 - y0 + 1) * (z1 - z0 + 1);
+  if (nc > c_grid_max_cells || nc <= 0) return false;
+  const GCell* tab = gtab + tr.grid_off;
+  const uint32_t* nx = gnext + tr.cmp_off;
+  for (int z = z0; z <= z1; ++z)
+    for (int y = y0; y <= y1; ++y)
+      for (int x = x0; x <= x1; ++x) {
+        const unsigned long long key = gkey(x, y, z);
+        uint32_t s = ghash(key) & tr.grid_mask;
+        uint32_t head = 0xFFFFFFFFu;
+        while (true) {
+          const uint4 e = __ldg(reinterpret_cast<const uint4*>(tab + s));
+          const unsigned long long ek = ((unsigned long long)e.y << 32) | e.x;
+          if (ek == key) {
+            head = e.z;
+            break;
+          }
+          if (ek == ~0ull) break;
+          s = (s + 1) & tr.grid_mask;
+        }
+        for (uint32_t l = head; l != 0xFFFFFFFFu; l = __ldg(nx + l)) {
+          const float4 p = __ldg(target + l);
+          const float d2 = sqd3(qx, qy, qz, p.x, p.y, p.z);
+          if (d2 < bd || (d2 == bd && l < bi)) {
+            bd = d2;
+            bi = l;
+            bp = p;
+          }
+        }
+      }
+  return true;
+}
+
 // ------------------------------------------------------------------------------------------------ exact 1-NN
 __device__ __forceinline__ float box_d2(float qx, float qy, float qz, const float4& lo, const float4& hi) {
   float dx = 0.f, dy = 0.f, dz = 0.f;
@@ -217,7 +303,8 @@ __device__ __forceinline__ bool visit(float d, float bd) { return d < INFINITY &
 // previous ICP iteration moves by millimetres, so its distance prunes nearly every subtree the cold search would still
 // enter.  The result is the same minimum of (distance, index) over the whole target either way.
 __device__ void nn_search(const TreeDev& tr, const Node2* __restrict__ nodes, const float4* __restrict__ tree_pts, float qx, float qy,
-                          float qz, float& bd, uint32_t& bi, float4& bp, int seed = -1, const float4* __restrict__ target = nullptr) {
+                          float qz, float& bd, uint32_t& bi, float4& bp, int seed = -1, const float4* __restrict__ target = nullptr,
+                          const GCell* __restrict__ gtab = nullptr, const uint32_t* __restrict__ gnext = nullptr, float ginv = 0.f) {
   bd = INFINITY;
   bi = kPadIdx;
   bp = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -227,6 +314,7 @@ __device__ void nn_search(const TreeDev& tr, const Node2* __restrict__ nodes, co
     bd = sqd3(qx, qy, qz, s.x, s.y, s.z);
     bi = (uint32_t)seed;
     bp = s;
+    if (gtab && tr.grid_mask && grid_probe(tr, gtab, gnext, target, ginv, qx, qy, qz, bd, bi, bp)) return;
   }
   const Node2* nd = nodes + tr.node_off;
   const float4* pts = tree_pts + tr.pts_off;
@@ -283,16 +371,39 @@ __device__ __forceinline__ void tf_f_sse(const float* T, float x, float y, float
 }
 
 // correspondence search + first-moment sums.  mode 0: ICP iteration, mode 1: fitness score pass.
+// phase 0: every point (seeded with its previous correspondence from the second iteration on).  The FIRST iteration has no
+// seeds and a cold tree walk costs twice a seeded one, so it runs in two launches: phase 1 searches every 8th point of the
+// curve order cold (warp 0 of each block takes the block's 32 samples), phase 2 searches the others seeded with the match
+// of their sample - a point a few decimetres from their own answer - and adds everybody's sums.  Seeds only ever supply
+// an initial candidate, so the result is the exact minimum of (distance, index) in every case.
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) k_icp_nn(PairDev* __restrict__ pairs, const uint32_t* __restrict__ blk2pair,
                                                    const float4* __restrict__ vox, float4* __restrict__ cur, int* __restrict__ match,
                                                    float* __restrict__ md2, const TreeDev* __restrict__ trees,
-                                                   const Node2* __restrict__ nodes, const float4* __restrict__ tree_pts, double max_d2) {
+                                                   const Node2* __restrict__ nodes, const float4* __restrict__ tree_pts, double max_d2,
+                                                   const GCell* __restrict__ gtab, const uint32_t* __restrict__ gnext, float ginv, int phase) {
   __shared__ long long s_red[kWarps][8];
   __shared__ float s_T[16];
   const uint32_t p = blk2pair[2 * blockIdx.x], first = blk2pair[2 * blockIdx.x + 1];
   PairDev& pr = pairs[p];
   if (MODE == 0 && !pr.active) return;
+  const TreeDev& tr = trees[pr.dst_job];
+  const float4* target = vox + tr.src_off;
+  if (MODE == 0 && phase == 1) {  // sample pass of the first iteration: no sums, 32 cold searches per block
+    if (threadIdx.x >= 32) return;
+    const uint32_t l = first + 8u * threadIdx.x;
+    if (l >= pr.src_pad_n) return;
+    const float4 s = __ldg(tree_pts + pr.src_pts_off + l);
+    if (__float_as_uint(s.w) == kPadIdx) return;
+    const size_t ci = (size_t)pr.cur_off + l;
+    float bd;
+    uint32_t bi;
+    float4 bp;
+    nn_search(tr, nodes, tree_pts, s.x, s.y, s.z, bd, bi, bp);
+    match[ci] = (bi != kPadIdx && !((double)bd > max_d2)) ? (int)bi : -1;
+    md2[ci] = bd;
+    return;
+  }
   if (threadIdx.x < 16) s_T[threadIdx.x] = (MODE == 0) ? pr.Tr[threadIdx.x] : pr.Tfinal[threadIdx.x];
   __syncthreads();
   const uint32_t l = first + threadIdx.x;
@@ -320,9 +431,17 @@ __global__ void __launch_bounds__(kBlock) k_icp_nn(PairDev* __restrict__ pairs, 
     float bd;
     uint32_t bi;
     float4 bp;
-    const TreeDev& tr = trees[pr.dst_job];
-    const int seed = pr.iters > 0 ? match[ci] : -1;  // written by the previous iteration of this pair
-    nn_search(tr, nodes, tree_pts, x, y, z, bd, bi, bp, seed, vox + tr.src_off);
+    if (MODE == 0 && phase == 2 && (l & 7u) == 0u) {  // searched by the sample pass
+      const int m = match[ci];
+      bd = md2[ci];
+      bi = m >= 0 ? (uint32_t)m : kPadIdx;
+      bp = m >= 0 ? __ldg(target + m) : make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      int seed = -1;
+      if (pr.iters > 0) seed = match[ci];  // written by the previous iteration of this pair
+      else if (phase == 2) seed = match[(size_t)pr.cur_off + (l & ~7u)];
+      nn_search(tr, nodes, tree_pts, x, y, z, bd, bi, bp, seed, target, gtab, gnext, ginv);
+    }
     if (MODE == 0) {
       const bool ok = bi != kPadIdx && !((double)bd > max_d2);
       match[ci] = ok ? (int)bi : -1;
@@ -633,12 +752,12 @@ static uint32_t pow2_ceil(uint32_t v) {
 }
 
 // builds one search tree per distinct target cloud of the batch
-static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs) {
+static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs, int n_targets) {
   const int nt = (int)tree_jobs.size();
   cudaStream_t s = c->stream;
   c->trees_host.assign(nt, TreeDev{});
   std::vector<uint32_t> offs(2 * (size_t)nt + 2, 0);  // [0, nt): compact offsets, [nt, 2nt): padded offsets
-  uint32_t cmp = 0, pad = 0, node = 0;
+  uint32_t cmp = 0, pad = 0, node = 0, gtot = 0;
   for (int t = 0; t < nt; ++t) {
     const GridDev& g = c->grids_host[tree_jobs[t]];
     TreeDev& tr = c->trees_host[t];
@@ -648,6 +767,14 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs) {
     tr.nleaf_pad = std::max<uint32_t>(2u, pow2_ceil(tr.nleaf));
     tr.pts_off = pad;
     tr.node_off = node;
+    tr.cmp_off = cmp;
+    tr.grid_off = gtot;
+    tr.grid_mask = 0;
+    if (c->use_grid && t < n_targets && tr.n > 0) {  // grids for the clouds that are searched (the sources are only ordered)
+      const uint32_t gcap = std::max<uint32_t>(16u, pow2_ceil(2u * tr.n));
+      tr.grid_mask = gcap - 1;
+      gtot += gcap;
+    }
     offs[t] = cmp;
     offs[nt + t] = pad;
     cmp += tr.n;
@@ -656,7 +783,8 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs) {
   }
   int rc;
   if ((rc = c->trees.ensure(std::max(nt, 1))) || (rc = c->blk2job.ensure(offs.size())) || (rc = c->tree_pts.ensure(std::max<uint32_t>(pad, 1))) ||
-      (rc = c->nodes.ensure(std::max<uint32_t>(node, 1))))
+      (rc = c->nodes.ensure(std::max<uint32_t>(node, 1))) || (rc = c->gtab.ensure(std::max<uint32_t>(gtot, 1))) ||
+      (rc = c->gnext.ensure(std::max<uint32_t>(cmp, 1))))
     return rc;
   if (nt == 0) return LOOP_OK;
   LOOP_CUDA(cudaMemcpyAsync(c->trees.p, c->trees_host.data(), sizeof(TreeDev) * nt, cudaMemcpyHostToDevice, s));
@@ -673,6 +801,11 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs) {
     need = std::max(need, sizeof(BoxAcc) * (size_t)nt);
     if ((rc = c->cub_tmp.ensure(need))) return rc;
     BoxAcc* acc = reinterpret_cast<BoxAcc*>(c->cub_tmp.p);
+    if (gtot) {
+      LOOP_CUDA(cudaMemsetAsync(c->gtab.p, 0xFF, sizeof(GCell) * (size_t)gtot, s));
+      k_tree_grid<<<grid_of(cmp, kBlock), kBlock, 0, s>>>(c->trees.p, cmp_off, nt, cmp, c->vox.p, c->gtab.p, c->gnext.p, 1.0f / c->grid_cell);
+      c->launches += 1;
+    }
     k_tree_box_init<<<grid_of(nt, 128), 128, 0, s>>>(acc, nt);
     k_tree_box<<<grid_of(cmp, kBlock), kBlock, 0, s>>>(c->trees.p, cmp_off, nt, cmp, c->vox.p, acc);
     k_tree_keys<<<grid_of(cmp, kBlock), kBlock, 0, s>>>(c->trees.p, cmp_off, nt, cmp, c->vox.p, acc, c->keys_a.p, c->vals_a.p, c->tree_order);
@@ -706,12 +839,17 @@ int run_icp(loop_ctx* c, const std::vector<PairHost>& ph, double score_thr, loop
       tree_of_job[p.dst_job] = (int)tree_jobs.size();
       tree_jobs.push_back(p.dst_job);
     }
+  const int n_targets = (int)tree_jobs.size();
+  if (const char* e = getenv("LOOP_GRID_MAXC")) {
+    const int v = std::max(1, atoi(e));
+    cudaMemcpyToSymbolAsync(c_grid_max_cells, &v, sizeof(int), 0, cudaMemcpyHostToDevice, s);
+  }
   for (const PairHost& p : ph)  // the source clouds go through the same ordering pass: their points are visited in Hilbert order
     if (tree_of_job[p.src_job] < 0) {
       tree_of_job[p.src_job] = (int)tree_jobs.size();
       tree_jobs.push_back(p.src_job);
     }
-  int rc = build_trees(c, tree_jobs);
+  int rc = build_trees(c, tree_jobs, n_targets);
   if (rc) return rc;
 
   c->pairs_host.assign(np, PairDev{});
@@ -754,8 +892,18 @@ int run_icp(loop_ctx* c, const std::vector<PairHost>& ph, double score_thr, loop
   for (int it = 0; it < prm.max_iter; ++it) {
     if (n_blocks) {
       tbegin(c, LT_NN);
-      k_icp_nn<0><<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->md2.p, c->trees.p, c->nodes.p,
-                                             c->tree_pts.p, prm.max_d2);
+      const float ginv = 1.0f / c->grid_cell;
+      const GCell* gt = c->use_grid ? c->gtab.p : nullptr;
+      if (it == 0 && c->sample_first) {
+        k_icp_nn<0><<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->md2.p, c->trees.p, c->nodes.p,
+                                               c->tree_pts.p, prm.max_d2, gt, c->gnext.p, ginv, 1);
+        k_icp_nn<0><<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->md2.p, c->trees.p, c->nodes.p,
+                                               c->tree_pts.p, prm.max_d2, gt, c->gnext.p, ginv, 2);
+        c->launches += 1;
+      } else {
+        k_icp_nn<0><<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->md2.p, c->trees.p, c->nodes.p,
+                                               c->tree_pts.p, prm.max_d2, gt, c->gnext.p, ginv, 0);
+      }
       tend(c);
       tbegin(c, LT_COV);
       k_icp_cov<<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->trees.p, prm.min_corr);
@@ -775,7 +923,7 @@ int run_icp(loop_ctx* c, const std::vector<PairHost>& ph, double score_thr, loop
   if (n_blocks) {
     tbegin(c, LT_SCORE);
     k_icp_nn<1><<<n_blocks, kBlock, 0, s>>>(c->pairs.p, c->blk2pair.p, c->vox.p, c->cur.p, c->match.p, c->md2.p, c->trees.p, c->nodes.p,
-                                           c->tree_pts.p, prm.max_d2);
+                                           c->tree_pts.p, prm.max_d2, c->use_grid ? c->gtab.p : nullptr, c->gnext.p, 1.0f / c->grid_cell, 0);
     tend(c);
     c->launches += 1;
   }

@@ -175,28 +175,87 @@ __global__ void __launch_bounds__(256) k_headpos(const uint32_t* __restrict__ fl
   if (i < n && flags[i]) head_pos[slot[i]] = i;
 }
 
-// one thread per OUTPUT voxel (every lane has work; the per-element form left 7 of 8 lanes idle at 8.5 points per voxel)
+// one thread per OUTPUT voxel (every lane has work; the per-element form left 7 of 8 lanes idle at 8.5 points per voxel).
+// A voxel's points are a contiguous run of the sorted order and MUST be added one after the other in that order (the f32
+// sums have to round like the sequential reference's), so a run is a serial chain.  Its end is known up front (the next
+// voxel's head), which takes the key comparison - a dependent load per point - out of the loop; runs longer than kLongRun
+// (the voxels next to the sensor collect thousands of returns from the 25 keyframes of a submap: one such run kept the
+// launch alive for 1.3 ms whatever the batch size) are handed to k_centroids_long.
+constexpr uint32_t kLongRun = 128;
+template <typename KeyT>
+__device__ __forceinline__ uint32_t run_end(const KeyT* __restrict__ keys, const uint32_t* __restrict__ head_pos, uint32_t v, uint32_t n_vox,
+                                            uint32_t i, uint32_t n) {
+  if (v + 1 < n_vox) return head_pos[v + 1];
+  const KeyT k = keys[i];  // last voxel: its run ends where the keys change (sentinel keys of non-finite points sort behind it)
+  uint32_t lo = i, hi = n;
+  while (lo + 1 < hi) {
+    const uint32_t mid = lo + (hi - lo) / 2;
+    if (keys[mid] == k) lo = mid; else hi = mid;
+  }
+  return hi;
+}
+
 template <typename KeyT>
 __global__ void __launch_bounds__(256) k_centroids(const KeyT* __restrict__ keys, const float4* __restrict__ sorted,
                                                    const uint32_t* __restrict__ flags, const uint32_t* __restrict__ slot,
-                                                   const uint32_t* __restrict__ head_pos, uint32_t n, float4* __restrict__ vox) {
+                                                   const uint32_t* __restrict__ head_pos, uint32_t n, float4* __restrict__ vox,
+                                                   uint32_t* __restrict__ long_list) {
   const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t n_vox = slot[n - 1] + flags[n - 1];
   if (v >= n_vox) return;
   const uint32_t i = head_pos[v];
-  const KeyT k = keys[i];
+  const uint32_t e = run_end(keys, head_pos, v, n_vox, i, n);
+  if (e - i > kLongRun) {
+    const uint32_t pos = atomicAdd(long_list, 1u);
+    long_list[1 + 2 * pos] = v;
+    long_list[2 + 2 * pos] = e;
+    return;
+  }
   float sx = 0.f, sy = 0.f, sz = 0.f, si = 0.f;
   uint32_t j = i;
-  do {
+  for (; j + 4 <= e; j += 4) {  // loads first, then the additions in order
+    const float4 p0 = sorted[j], p1 = sorted[j + 1], p2 = sorted[j + 2], p3 = sorted[j + 3];
+    sx = sx + p0.x; sy = sy + p0.y; sz = sz + p0.z; si = si + p0.w;
+    sx = sx + p1.x; sy = sy + p1.y; sz = sz + p1.z; si = si + p1.w;
+    sx = sx + p2.x; sy = sy + p2.y; sz = sz + p2.z; si = si + p2.w;
+    sx = sx + p3.x; sy = sy + p3.y; sz = sz + p3.z; si = si + p3.w;
+  }
+  for (; j < e; ++j) {
     const float4 p = sorted[j];
-    sx = sx + p.x;
-    sy = sy + p.y;
-    sz = sz + p.z;
-    si = si + p.w;
-    ++j;
-  } while (j < n && keys[j] == k);
-  const float cnt = (float)(j - i);
+    sx = sx + p.x; sy = sy + p.y; sz = sz + p.z; si = si + p.w;
+  }
+  const float cnt = (float)(e - i);
   vox[v] = make_float4(sx / cnt, sy / cnt, sz / cnt, si / cnt);
+}
+
+// one warp per long run: 32 points per coalesced load (the next chunk is in flight while this one is added), the additions
+// still strictly in run order (every lane carries the same sums; lane 0 writes)
+__global__ void __launch_bounds__(256) k_centroids_long(const float4* __restrict__ sorted, const uint32_t* __restrict__ head_pos,
+                                                        const uint32_t* __restrict__ long_list, float4* __restrict__ vox) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t n_long = long_list[0];
+  for (uint32_t r = warp; r < n_long; r += n_warps) {
+    const uint32_t v = long_list[1 + 2 * r], e = long_list[2 + 2 * r];
+    const uint32_t i = head_pos[v];
+    float sx = 0.f, sy = 0.f, sz = 0.f, si = 0.f;
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 p = (i + lane < e) ? sorted[i + lane] : zero;
+    for (uint32_t j0 = i; j0 < e; j0 += 32) {
+      const uint32_t jn = j0 + 32 + lane;
+      const float4 nxt = (jn < e) ? sorted[jn] : zero;
+      const int cnt = (int)min(32u, e - j0);
+      for (int t = 0; t < cnt; ++t) {
+        sx = sx + __shfl_sync(0xFFFFFFFFu, p.x, t);
+        sy = sy + __shfl_sync(0xFFFFFFFFu, p.y, t);
+        sz = sz + __shfl_sync(0xFFFFFFFFu, p.z, t);
+        si = si + __shfl_sync(0xFFFFFFFFu, p.w, t);
+      }
+      p = nxt;
+    }
+    const float cnt = (float)(e - i);
+    if (lane == 0) vox[v] = make_float4(sx / cnt, sy / cnt, sz / cnt, si / cnt);
+  }
 }
 
 // output ranges of the jobs in the voxelised buffer
@@ -286,10 +345,14 @@ static int voxelize_raw(loop_ctx* c, const std::vector<JobDev>& jd, const SegDev
     k_gather_sorted<<<grid_of(n_raw, 256), 256, 0, s>>>(c->vals_b.p, n_raw, c->raw.p, c->cur.p);
     k_headpos<<<grid_of(n_raw, 256), 256, 0, s>>>(c->vals_a.p, c->head_scan.p, n_raw, c->vals_b.p);  // vals_b was consumed by the gather
     // the voxel count is only known on the device: launch for the upper bound n_raw / 1 and let the surplus threads exit
-    if (narrow) k_centroids<uint32_t><<<grid_of(n_raw, 256), 256, 0, s>>>(kb32, c->cur.p, c->vals_a.p, c->head_scan.p, c->vals_b.p, n_raw, c->vox.p);
-    else k_centroids<unsigned long long><<<grid_of(n_raw, 256), 256, 0, s>>>(c->keys_b.p, c->cur.p, c->vals_a.p, c->head_scan.p, c->vals_b.p, n_raw, c->vox.p);
+    // list of the long runs: counter + (voxel, end) pairs in the sort's input key buffer, which is free by now (2 * n_raw / kLongRun + 1 words)
+    uint32_t* long_list = reinterpret_cast<uint32_t*>(c->keys_a.p);
+    LOOP_CUDA(cudaMemsetAsync(long_list, 0, sizeof(uint32_t), s));
+    if (narrow) k_centroids<uint32_t><<<grid_of(n_raw, 256), 256, 0, s>>>(kb32, c->cur.p, c->vals_a.p, c->head_scan.p, c->vals_b.p, n_raw, c->vox.p, long_list);
+    else k_centroids<unsigned long long><<<grid_of(n_raw, 256), 256, 0, s>>>(c->keys_b.p, c->cur.p, c->vals_a.p, c->head_scan.p, c->vals_b.p, n_raw, c->vox.p, long_list);
+    k_centroids_long<<<c->n_sms * 4, 256, 0, s>>>(c->cur.p, c->vals_b.p, long_list, c->vox.p);
     k_job_ranges<<<1, 32, 0, s>>>(c->grids.p, n_jobs, c->vals_a.p, c->head_scan.p, n_raw);
-    c->launches += 10;  // keys/heads/gather/headpos/centroids/ranges + the library sort and scan passes (counted as one each)
+    c->launches += 11;  // keys/heads/gather/headpos/centroids (2)/ranges + the library sort and scan passes (counted as one each)
   }
   tend(c);
   LOOP_CUDA(cudaGetLastError());

@@ -280,3 +280,71 @@ class LoopClosure:
         self._check(self.lib.loop_batch_stats(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return dict(iterations=a.value, src_points=b.value, nn_queries=c.value)
 
+
+
+class LoopClosurePool:
+    """Several LoopClosure contexts on ONE GPU (own stream and workspace each, the keyframe store replicated), driven from
+    host threads: a batch of candidate pairs is cut into contiguous parts that are verified concurrently.  Candidate pairs are
+    independent (loop_closure.cpp:101-126), so the results are those of a single context; what the pool buys is overlap - the
+    short, latency-bound stretches of one part (VoxelGrid bookkeeping, tree build, the last ICP iterations of a few straggler
+    pairs, host round trips) run under the wide correspondence-search kernels of the other.  That matters most when a rank
+    holds few pairs (8-GPU sharding of a 256-pair batch)."""
+
+    def __init__(self, n_ctx=2, **kw):
+        self.ctx = [LoopClosure(**kw) for _ in range(max(1, int(n_ctx)))]
+
+    def close(self):
+        for c in self.ctx:
+            c.close()
+
+    def add_keyframe(self, xyzi, pose_corrected, stamp=0.0):
+        idx = -1
+        for c in self.ctx:
+            idx = c.add_keyframe(xyzi, pose_corrected, stamp)
+        return idx
+
+    def clear(self):
+        for c in self.ctx:
+            c.clear()
+
+    def split(self, n):
+        """[lo, hi) of each context's contiguous part of an n-pair list."""
+        return [shard_pairs(n, k, len(self.ctx)) for k in range(len(self.ctx))]
+
+    def make_arrays(self, pairs):
+        """ctypes pair / result arrays, one set per context (caller-owned, reusable across calls)."""
+        out = []
+        for lo, hi in self.split(len(pairs)):
+            n = hi - lo
+            arr = (LoopPair * max(n, 1))()
+            for i, (a, b) in enumerate(pairs[lo:hi]):
+                arr[i].src_idx, arr[i].dst_idx = int(a), int(b)
+            out.append((arr, n, (LoopResult * max(n, 1))()))
+        return out
+
+    def verify_arrays(self, arrays):
+        """One loop_verify_batch per context, concurrently (the C call releases the GIL and ends with its stream synchronised)."""
+        import threading
+
+        errs = []
+
+        def run(c, a):
+            try:
+                if a[1]:
+                    c.verify_batch_raw(a[0], a[1], a[2])
+            except Exception as e:  # surfaced below: a failed part must fail the batch
+                errs.append(e)
+
+        th = [threading.Thread(target=run, args=(c, a)) for c, a in zip(self.ctx[1:], arrays[1:])]
+        for t in th:
+            t.start()
+        run(self.ctx[0], arrays[0])
+        for t in th:
+            t.join()
+        if errs:
+            raise errs[0]
+
+    def verify_batch(self, pairs):
+        arrays = self.make_arrays(pairs)
+        self.verify_arrays(arrays)
+        return [_result(res[i]) for arr, n, res in arrays for i in range(n)]
