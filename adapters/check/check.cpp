@@ -50,6 +50,17 @@ int main() {
     RegistrationOutput r2 = strict.performLoopClosure(kfs[2], kfs, 0);
     std::printf("adapters: gated out: converged=%d valid=%d score=%g\n", (int)r2.is_converged_, (int)r2.is_valid_, r2.score_);
     if (r2.is_valid_ || r2.is_converged_ || !(r2.score_ < 1e300)) throw std::runtime_error("RegistrationOutput flags differ from loop_closure.cpp:85-90");
+    // pose sync sends only what changed; batched candidate generation; ingest from the world-frame cloud
+    kfs[1].pose_corrected_eig_(1, 3) = 0.02;
+    std::vector<int> cl = lc.fetchClosestKeyframeIdxBatch({3, 2, 0}, kfs);
+    if (cl.size() != 3 || cl[0] != lc.fetchClosestKeyframeIdx(kfs[3], kfs) || cl[2] != -1) throw std::runtime_error("fetchClosestKeyframeIdxBatch differs");
+    LoopClosureB200 ingest(cfg);
+    Eigen::Matrix4d pose = Eigen::Matrix4d::Identity();
+    pose(0, 3) = 1.5, pose(1, 3) = -0.5;
+    pcl::PointCloud<PointType> shifted = world;
+    for (auto &p : shifted.points) p.x += 1.5f, p.y -= 0.5f;  // the same cloud as published in the world frame
+    if (ingest.addKeyframeFromWorldCloud(shifted, pose, 0.0) != 0) throw std::runtime_error("addKeyframeFromWorldCloud index");
+    std::printf("adapters: batch candidates %d %d %d, world ingest ok\n", cl[0], cl[1], cl[2]);
   } catch (const std::exception &e) {
     std::printf("adapters: FAILED: %s\n", e.what());
     return 1;

@@ -6,6 +6,7 @@
 // Requires the reference's own headers first (PointType, PosePcd, LoopClosureConfig, RegistrationOutput, PcdPair);
 // adapters/check/ compiles it against minimal stand-ins because PCL/Eigen are not installed in this image.
 #pragma once
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -17,6 +18,7 @@ class LoopClosureB200 {
   LoopClosureConfig config_;
   int closest_keyframe_idx_ = -1;
   size_t uploaded_ = 0;  // keyframes already resident on the device
+  std::vector<double> sent_pose_;  // 16 doubles per resident keyframe: the pose_corrected_eig_ the device holds
   pcl::PointCloud<PointType> src_cloud_, dst_cloud_, aligned_;
 
   static void pack(const pcl::PointCloud<PointType> &c, std::vector<float> &out) {  // PointXYZI (32 B) -> 4 floats
@@ -39,23 +41,34 @@ class LoopClosureB200 {
   void check(int rc, const char *what) const {
     if (rc != LOOP_OK) throw std::runtime_error(std::string(what) + ": " + loop_last_error());
   }
-  // keyframes_ only grows and only pose_corrected_eig_ changes (fast_lio_sam.cpp pose-graph update): mirror both
+  // keyframes_ only grows and only pose_corrected_eig_ changes (fast_lio_sam.cpp pose-graph update): mirror both.  Poses are
+  // compared with what the device already holds and only the changed ones are sent, in ONE call (a tick without a pose-graph
+  // update sends nothing; round 1 re-sent every pose on every call, O(K) C calls per loop check).
   void sync(const std::vector<PosePcd> &keyframes) {
     std::vector<float> buf;
     double T[16];
     if (keyframes.size() < uploaded_) {
       check(loop_keyframe_clear(ctx_), "loop_keyframe_clear");
       uploaded_ = 0;
+      sent_pose_.clear();
     }
+    std::vector<int> changed;
+    std::vector<double> poses;
     for (size_t i = 0; i < uploaded_; ++i) {
       pose16(keyframes[i].pose_corrected_eig_, T);
-      check(loop_keyframe_set_pose(ctx_, (int)i, T), "loop_keyframe_set_pose");
+      if (std::memcmp(T, &sent_pose_[16 * i], sizeof(T)) != 0) {
+        changed.push_back((int)i);
+        poses.insert(poses.end(), T, T + 16);
+        std::memcpy(&sent_pose_[16 * i], T, sizeof(T));
+      }
     }
+    if (!changed.empty()) check(loop_keyframe_set_poses(ctx_, changed.data(), poses.data(), (int)changed.size()), "loop_keyframe_set_poses");
     for (; uploaded_ < keyframes.size(); ++uploaded_) {
       const PosePcd &k = keyframes[uploaded_];
       pack(k.pcd_, buf);
       pose16(k.pose_corrected_eig_, T);
       check(loop_keyframe_add(ctx_, buf.data(), (int)k.pcd_.size(), T, k.timestamp_, nullptr), "loop_keyframe_add");
+      sent_pose_.insert(sent_pose_.end(), T, T + 16);
     }
   }
   RegistrationOutput to_output(const loop_result &r) const {  // loop_closure.cpp:83-90
@@ -94,12 +107,17 @@ class LoopClosureB200 {
   PcdPair setSrcAndDstCloud(const std::vector<PosePcd> &keyframes, const int src_idx, const int dst_idx, const int submap_range,
                             const double voxel_res) {
     sync(keyframes);
+    // a voxelised submap never has more points than the keyframes it is made of: one call with buffers sized from those
+    size_t cap = 0;
+    for (const int centre : {src_idx, dst_idx}) {
+      size_t n = 0;
+      for (int i = centre - submap_range; i < centre + submap_range + 1; ++i)
+        if (i >= 0 && i < static_cast<int>(keyframes.size()) - 1) n += keyframes[i].pcd_.size();
+      cap = n > cap ? n : cap;
+    }
     int ns = 0, nd = 0;
-    check(loop_set_src_dst(ctx_, src_idx, dst_idx, submap_range, (float)voxel_res, nullptr, &ns, nullptr, &nd, 0), "loop_set_src_dst");
-    std::vector<float> s((size_t)ns * 4 + 4), d((size_t)nd * 4 + 4);
-    const int cap = ns > nd ? ns : nd;
-    s.resize((size_t)cap * 4 + 4), d.resize((size_t)cap * 4 + 4);
-    check(loop_set_src_dst(ctx_, src_idx, dst_idx, submap_range, (float)voxel_res, s.data(), &ns, d.data(), &nd, cap), "loop_set_src_dst");
+    std::vector<float> s(cap * 4 + 4), d(cap * 4 + 4);
+    check(loop_set_src_dst(ctx_, src_idx, dst_idx, submap_range, (float)voxel_res, s.data(), &ns, d.data(), &nd, (int)cap), "loop_set_src_dst");
     pcl::PointCloud<PointType> sc, dc;
     unpack(s, ns, sc);
     unpack(d, nd, dc);
@@ -130,6 +148,29 @@ class LoopClosureB200 {
     check(loop_verify_batch(ctx_, &p, 1, config_.num_submap_keyframes_, (float)config_.voxel_res_, config_.icp_score_threshold_, &r),
           "loop_verify_batch");
     return to_output(r);
+  }
+  // NEW (no reference counterpart): fetchClosestKeyframeIdx for several query keyframes in one device launch
+  std::vector<int> fetchClosestKeyframeIdxBatch(const std::vector<int> &query_indices, const std::vector<PosePcd> &keyframes) {
+    sync(keyframes);
+    std::vector<int> out(query_indices.size(), -1);
+    check(loop_fetch_closest_batch(ctx_, query_indices.data(), (int)query_indices.size(), config_.loop_detection_radius_,
+                                   config_.loop_detection_timediff_threshold_, out.data()),
+          "loop_fetch_closest_batch");
+    return out;
+  }
+  // NEW: ingest of a keyframe straight from the WORLD-frame cloud FAST-LIO publishes (what PosePcd's constructor receives,
+  // pose_pcd.hpp:25-43): the pose^-1 re-expression runs on the device, the host never transforms or copies the cloud.  Must be
+  // called in keyframe order, for the keyframe that is about to be appended to keyframes_ (index == keyframes_.size()).
+  int addKeyframeFromWorldCloud(const pcl::PointCloud<PointType> &cloud_world, const Eigen::Matrix4d &pose, double stamp) {
+    std::vector<float> buf;
+    double T[16];
+    pack(cloud_world, buf);
+    pose16(pose, T);
+    int idx = -1;
+    check(loop_keyframe_add_world(ctx_, buf.data(), (int)cloud_world.size(), T, stamp, &idx), "loop_keyframe_add_world");
+    uploaded_ = (size_t)idx + 1;
+    sent_pose_.insert(sent_pose_.end(), T, T + 16);
+    return idx;
   }
   // NEW (no reference counterpart): all candidates of a timer tick in one device batch
   std::vector<RegistrationOutput> performLoopClosureBatch(const std::vector<PosePcd> &keyframes, const std::vector<loop_pair> &pairs) {

@@ -50,11 +50,13 @@ def parse():
     ap.add_argument("--n-pass", type=int, default=100, help="loop workload: keyframes per pass of the out-and-back drive")
     ap.add_argument("--sweep-map", type=int, default=20_000_000, help="knn_sweep workload: map points")
     ap.add_argument("--sweep-queries", type=int, default=100_000, help="knn_sweep workload: queries per call")
+    ap.add_argument("--sweep-big-queries", type=int, default=1_000_000, help="knn_sweep workload: queries per call of the extra rows at filter_size_map 0.5 (0: skip)")
     ap.add_argument("--seq-scans", type=int, default=100, help="sequence workload: VLP-16 scans (configs[0] names 1000)")
     ap.add_argument("--map-scans", type=int, default=200, help="map_growth workload: Avia-shaped scans along the drive")
     ap.add_argument("--map-check-every", type=int, default=50, help="map_growth workload: compare the live set with the oracle every N scans")
     ap.add_argument("--no-loop", action="store_true", help="iekf workload: skip the loop_icp section of the JSON line")
     ap.add_argument("--no-parity", action="store_true", help="iekf workload: skip the oracle-vs-GPU comparison at the full config")
+    ap.add_argument("--no-configs", action="store_true", help="iekf workload: skip the short runs of configs[0] / [2] / [4] folded into the JSON line")
     return ap.parse_args()
 
 
@@ -434,12 +436,60 @@ def run_ours(args, synth):
                                     "ms_per_step": r["ms_per_step"]}
         if loop_out is not None:
             line["loop_icp"] = loop_out
-        print(json.dumps(line), flush=True)
     g.close()
+    if rank == 0:
+        if world == 1 and not args.no_configs:
+            line["configs"] = compact_configs(args)
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     if parity is not None and not parity["all"]:
         raise SystemExit("bench.py: the GPU path differs from the oracle at the BASELINE config: " + json.dumps(parity))
+
+
+def compact_configs(args):
+    """Short runs of the other BASELINE.json configs, folded into the headline line so that the driver-run record carries all
+    five (the full-size runs are the standalone workloads: --workload sequence / map_growth / knn_sweep / loop).  Each entry:
+    value, cpu_baseline, parity flag, roofline fraction where the workload has one.  Bounded to about half a minute."""
+    import copy
+
+    out = {}
+    t0 = time.perf_counter()
+    a = copy.copy(args)
+    a.seq_scans = 30
+    try:
+        r = importlib.import_module("bench_seq").run(a)
+        out["configs[0] sequence"] = {"value": r["value"], "unit": r["unit"], "scans": r["config"]["scans"], "full_size": "--workload sequence --seq-scans 1000",
+                                      "cpu_baseline": r["cpu_baseline"]["value"], "ate_difference_m": r["ate_difference_m"],
+                                      "divergence_max_m": r["trajectory_divergence_max_m"], "parity": bool(r["ate_difference_m"] < r["bar_m"])}
+    except Exception as e:  # a short run must not take the headline line down with it
+        out["configs[0] sequence"] = {"error": str(e)[:200]}
+    a = copy.copy(args)
+    a.map_scans, a.map_check_every = 41, 20
+    try:
+        r = importlib.import_module("bench_map").run(a)
+        out["configs[2] map_growth"] = {"value": r["value"], "unit": r["unit"], "scans": r["config"]["scans"], "full_size": "--workload map_growth --map-scans 2001",
+                                        "cpu_baseline": r["cpu_baseline"]["value"], "parity": bool(r["live_set_identical_to_oracle"]),
+                                        "roofline_frac": r["roofline"]["frac"]}
+    except Exception as e:
+        out["configs[2] map_growth"] = {"error": str(e)[:200]}
+    a = copy.copy(args)
+    a.steps = 3
+    try:
+        r = importlib.import_module("bench_sweep").run(a, spacings=(0.5,))
+        row = r["sweep"][0]
+        big = {b["query_set"]: b for b in r["sweep_1M"]}
+        out["configs[4] knn_sweep"] = {"value": row["queries_per_s"], "unit": "queries/s", "map_points": r["config"]["map_points"], "filter_size_map": 0.5,
+                                       "full_size": "--workload knn_sweep (four densities)", "parity": bool(row["exact_on_sample"] and all(b["exact_on_sample"] for b in big.values())),
+                                       "fraction_of_gather_probe_100k": row["fraction_of_gather_probe_16B"],
+                                       "queries_per_s_1M_patch": big["patch"]["queries_per_s"], "fraction_of_gather_probe_1M_patch": big["patch"]["fraction_of_gather_probe_16B"],
+                                       "queries_per_s_1M_spread_l2_flushed": big["spread"]["queries_per_s_l2_flushed"],
+                                       "fraction_of_gather_probe_1M_spread": big["spread"]["fraction_of_gather_probe_16B"],
+                                       "gather_probe_GBps_16B": r["gather_probe"]["GBps_16B_requests"]}
+    except Exception as e:
+        out["configs[4] knn_sweep"] = {"error": str(e)[:200]}
+    out["seconds"] = time.perf_counter() - t0
+    return out
 
 
 def main():

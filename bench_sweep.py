@@ -41,10 +41,16 @@ def make_density_map(n_points, spacing, seed=7):
     return np.ascontiguousarray(m + jit), L
 
 
-def make_queries(m, n_q, seed=11):
-    """Scan-like queries: the n_q/2 map points closest to the origin (a dense local patch, as the near field of a LiDAR
-    scan is), each observed twice with 3 cm noise; returned in random order (the library sorts them itself)."""
+def make_queries(m, n_q, seed=11, mode="patch"):
+    """Scan-like queries, returned in random order (the library sorts them itself).
+    patch : the n_q/2 map points closest to the origin (a dense local patch, as the near field of a LiDAR scan is), each
+            observed twice with 3 cm noise - the touched part of the map fits the 126 MB L2;
+    spread: n_q map points drawn uniformly from the WHOLE 20M-point map, 3 cm noise - neighbouring queries are metres apart,
+            every query stages its own 27 cells, and the touched part of the map is far larger than L2 (the HBM-bound regime)."""
     rng = np.random.default_rng(seed)
+    if mode == "spread":
+        pick = rng.integers(0, len(m), n_q)
+        return np.ascontiguousarray(m[pick] + rng.normal(0, 0.03, (n_q, 3)).astype(np.float32))
     r2 = m[:, 0] ** 2 + m[:, 1] ** 2
     k = min(len(m), (n_q + 1) // 2)
     near = np.argpartition(r2, k - 1)[:k]
@@ -53,61 +59,87 @@ def make_queries(m, n_q, seed=11):
     return np.ascontiguousarray(q[rng.permutation(n_q)])
 
 
-def main(args):
+def run_case(g, m, q, reps, flush, torch):
+    n_q = len(q)
+    ids, d2, _, cnt = g.map_knn(q, 5, 5.0)  # warm-up + result for the exactness sample
+
+    def timed(fl):
+        g.timing(True)
+        g.timing_reset()
+        for r in range(reps):
+            if fl is not None:
+                fl.fill_(r & 255)  # evict the map from L2 between calls
+                torch.cuda.synchronize()
+            g.map_knn(q, 5, 5.0)
+        ms_ = {k: g.timing_get(k)[0] for k in ("knn", "sort")}  # CUDA events per call: search kernels / ordering kernels
+        g.timing(False)
+        return ms_
+
+    f0 = g.knn_stats_detail()
+    t = timed(None)
+    f1 = g.knn_stats_detail()
+    tc = timed(flush)
+    rng = np.random.default_rng(3)
+    ok = True
+    for i in rng.integers(0, n_q, 16):  # exactness at full size: brute force on a sample
+        d = m - q[i]
+        dd = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+        cand = np.flatnonzero(dd <= 5.0)
+        order = cand[np.lexsort((cand, dd[cand]))][:5]
+        ok &= int(cnt[i]) == len(order) and np.array_equal(ids[i, : len(order)], order.astype(np.uint32))
+    ms, msc = t["knn"] + t["sort"], tc["knn"] + tc["sort"]  # a call = ordering kernels + search kernels
+    return {"queries": n_q, "knn_ms": ms, "knn_ms_l2_flushed": msc, "order_ms": t["sort"], "search_ms": t["knn"], "search_ms_l2_flushed": tc["knn"], "queries_per_s": n_q / (ms * 1e-3),
+            "queries_per_s_l2_flushed": n_q / (msc * 1e-3), "algorithmic_GBps": ALGO_BYTES_PER_QUERY * n_q / (ms * 1e-3) / 1e9,
+            "algorithmic_GBps_l2_flushed": ALGO_BYTES_PER_QUERY * n_q / (msc * 1e-3) / 1e9,
+            "per_query_kernel_fraction": (f1["per_query"] - f0["per_query"]) / reps / n_q,
+            "sub_tile_task_fraction": (f1["incoherent"] - f0["incoherent"]) / reps / n_q, "mean_found": float(cnt.mean()), "exact_on_sample": bool(ok)}
+
+
+def run(args, spacings=(1.0, 0.5, 0.25, 0.125)):
+    """Returns the JSON line as a dict (bench.py folds a one-density run of it into the headline line)."""
     pkg = importlib.import_module("fast-lio-sam_gps_b200")
     n_map, n_q = args.sweep_map, args.sweep_queries
     import torch
 
-    rows = []
+    rows, big = [], []
     probe = None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    for spacing in (1.0, 0.5, 0.25, 0.125):
+    reps = max(3, args.steps)
+    n_big = int(getattr(args, "sweep_big_queries", 1_000_000))
+    for spacing in spacings:
         m, L = make_density_map(n_map, spacing)
-        q = make_queries(m, n_q)
-        g = pkg.LioContext(spacing, max_points=n_map + (1 << 20), max_scan=max(n_q, 1 << 17))  # filter_size_map = spacing: cell = 2 x spacing
+        g = pkg.LioContext(spacing, max_points=n_map + (1 << 20), max_scan=max(n_q, n_big if spacing == 0.5 else 0, 1 << 17))  # cell = 2 x spacing
         if probe is None:
             probe = g.gather_probe(320 << 20, 5)
         t0 = time.perf_counter()
         g.map_build(m)
         g.sync()
         build_s = time.perf_counter() - t0
-        ids, d2, _, cnt = g.map_knn(q, 5, 5.0)  # warm-up + result for the exactness sample
-        def timed(flush):
-            g.timing(True)
-            g.timing_reset()
-            for r in range(reps):
-                if flush is not None:
-                    flush.fill_(r & 255)  # evict the map from L2 between calls
-                    torch.cuda.synchronize()
-                g.map_knn(q, 5, 5.0)
-            ms_, _ = g.timing_get("knn")  # CUDA events around sort + search, per call
-            g.timing(False)
-            return ms_
-
-        reps = max(3, args.steps)
-        f0 = g.knn_fallback_queries()
-        ms = timed(None)
-        left = (g.knn_fallback_queries() - f0) / reps
-        ms_cold = timed(flush)
-        # exactness at full size: brute force on a sample
-        rng = np.random.default_rng(3)
-        ok = True
-        for i in rng.integers(0, n_q, 24):
-            d = m - q[i]
-            dd = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
-            cand = np.flatnonzero(dd <= 5.0)
-            order = cand[np.lexsort((cand, dd[cand]))][:5]
-            ok &= int(cnt[i]) == len(order) and np.array_equal(ids[i, : len(order)], order.astype(np.uint32))
-        rows.append({"filter_size_map": spacing, "extent_m": round(float(L), 1), "knn_ms": ms, "knn_ms_l2_flushed": ms_cold, "queries_per_s": n_q / (ms * 1e-3),
-                     "queries_per_s_l2_flushed": n_q / (ms_cold * 1e-3),
-                     "algorithmic_GBps": ALGO_BYTES_PER_QUERY * n_q / (ms * 1e-3) / 1e9, "deferred_fraction": left / n_q,
-                     "mean_found": float(cnt.mean()), "map_build_s": build_s, "exact_on_sample": bool(ok)})
+        r = run_case(g, m, make_queries(m, n_q), reps, flush, torch)
+        r.update({"filter_size_map": spacing, "extent_m": round(float(L), 1), "map_build_s": build_s, "query_set": "patch"})
+        rows.append(r)
+        if spacing == 0.5 and n_big > 0:
+            # the same map with ten times the queries per launch (is the launch too small, or the kernel too slow?), and with the
+            # queries spread over the whole map (the working set leaves L2: the HBM-bound regime)
+            for mode in ("patch", "spread"):
+                rb = run_case(g, m, make_queries(m, n_big, mode=mode), reps, flush, torch)
+                rb.update({"filter_size_map": spacing, "query_set": mode,
+                           "fraction_of_gather_probe_16B": rb["algorithmic_GBps_l2_flushed" if mode == "spread" else "algorithmic_GBps"] / probe[0]})
+                big.append(rb)
         g.close()
-        del m, q
-    line = {"metric": "exact k=5 NN queries/s (20M-point map)", "unit": "queries/s", "value": max(r["queries_per_s"] for r in rows),
+        del m
+    for r in rows:
+        r["fraction_of_gather_probe_16B"] = r["algorithmic_GBps"] / probe[0]
+    line = {"metric": "exact k=5 NN queries/s (20M-point map)", "unit": "queries/s", "value": max(r["queries_per_s"] for r in rows + big),
             "n_gpus": 1, "higher_is_better": True, "data": "synthetic", "dtype": "f32",
             "config": {"workload": "configs[4]: large-map stress, kNN throughput sweep over map density", "map_points": n_map,
-                       "queries": n_q, "k": 5, "max_sqdist": 5.0, "timing": "CUDA events around sort + search per call (queries resident)"},
-            "gather_probe": {"table_bytes": 320 << 20, "GBps_16B_requests": probe[0], "GBps_32B_sectors": probe[1]},
-            "sweep": rows}
-    print(json.dumps(line))
+                       "queries": n_q, "queries_big": n_big, "k": 5, "max_sqdist": 5.0,
+                       "timing": "CUDA events per call, queries resident: knn_ms = ordering kernels (order_ms) + search kernels (search_ms)"},
+            "gather_probe": {"table_bytes": 320 << 20, "GBps_16B_requests": probe[0], "GBps_32B_sectors": probe[1],
+                             "what": "random 16-byte loads from a 320 MB table: the achievable gather ceiling the fractions refer to"},
+            "sweep": rows, "sweep_1M": big}
+    return line
+
+
+def main(args):
+    print(json.dumps(run(args)))

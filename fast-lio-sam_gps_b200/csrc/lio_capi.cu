@@ -616,8 +616,10 @@ int lio_map_incremental(lio_ctx* c, const double* state, int flg_ekf_inited, int
     return LIO_E_STATE;
   }
   if (!c->nn_valid) {
-    // no search has run for this scan: every point is treated as having no neighbours (reference: empty Nearest_Points)
-    LIO_CUDA(cudaMemsetAsync(c->nn_cnt, 0, sizeof(int) * (size_t)c->scan_n, c->stream));
+    // no search has run for this scan: Nearest_Points[i] is empty for every point (reference: `!Nearest_Points[i].empty()` is
+    // false -> PointToAdd).  nn_cnt = -1 says exactly that; 0 would mean "searched, nothing within max_sqdist", for which
+    // map_incremental looks up the far nearest neighbour.
+    LIO_CUDA(cudaMemsetAsync(c->nn_cnt, 0xFF, sizeof(int) * (size_t)c->scan_n, c->stream));
   }
   rc = scan_classify_insert(c, state, flg_ekf_inited);
   if (rc) return rc;

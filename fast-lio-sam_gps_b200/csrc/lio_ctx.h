@@ -78,6 +78,8 @@ struct lio_ctx {
   int* nn_cnt = nullptr;    // max_scan
   uint8_t* sel = nullptr;   // max_scan
   float4* plane = nullptr;  // max_scan: a b c pd2
+  float4* far_nn = nullptr;       // max_scan: unbounded nearest map point of the scan points whose search found none within max_sqdist (k_far_nn)
+  double* knn_state_dev = nullptr;  // 36 doubles: the state of the last search of the scan (written by the search kernel)
   float4* pfit = nullptr;   // max_scan: a b c d of the plane fitted at the last search (a = NaN: no valid plane)
   double* rows = nullptr;   // max_scan * 13, allocated on first lio_h_share_rows
   uint8_t* cls = nullptr;   // map_incremental class per point
@@ -93,6 +95,7 @@ struct lio_ctx {
   void* sort_scratch = nullptr;  // SortScratch (lio_scan.cu): coarse-bin histogram / offsets / cursors of the scan ordering
   uint32_t tile_cap = 0;
   bool order_valid = false;      // tile_vals[1] holds the order of the current scan
+  double sort_state[36]{};         // the state the current order was computed at
   bool resort_each_search = true;  // the curve order is recomputed at the state of every search (LIO_RESORT=0: once per scan)
   std::vector<std::pair<int, void*>> sort_graphs;  // (padded size, cudaGraphExec_t) of the captured keys + sort passes
   bool sort_graph_ok = true;     // false after a failed capture (LIO_SORT_GRAPH=0 disables it up front)

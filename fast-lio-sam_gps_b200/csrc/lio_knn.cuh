@@ -491,4 +491,109 @@ __device__ void knn_search_warp(const MapView& m, WarpList& wl, float qx, float 
   }
 }
 
+// ------------------------------------------------------------------------------------------------ unbounded 1-NN
+// Nearest live map point of q with NO distance bound (upstream's Nearest_Search is unbounded: a scan point whose 5-NN search
+// found nothing within max_d2 still has its far nearest neighbour at the head of Nearest_Points[i], and map_incremental
+// reads it).  One warp per query; rare path (points in front of the mapped area).  Shells of 4x4x4-cell blocks around the
+// query are walked through the occupancy words - a lane per block, the set bits name the cells worth probing - until the
+// best distance is inside the searched cube; when kFarRings shells (32 m at 1 m cells) hold nothing, every bucket of the
+// pool is scanned.  Result: key (d2 bits << 32 | id, ~0: the map is empty) and slot, the same in every lane.
+constexpr int kFarRings = 8;
+__device__ __forceinline__ void far_scan_cell(const MapView& m, int cx, int cy, int cz, float qx, float qy, float qz, unsigned long long& best,
+                                              uint32_t& bref) {
+  const unsigned long long key = pack3(cx, cy, cz);
+  const HashEntry e = table_find(m, key);
+  if (e.key != key) return;
+  for (uint32_t b = e.head; b != kNone; b = chain_next(m, e.head, e.ovf, b)) {
+    if (b >= m.pool_cap) break;  // null bucket of a cell created under pool exhaustion
+#pragma unroll
+    for (int j = 0; j < kSlots; ++j) {
+      const float4 p = __ldg(m.slots + (size_t)b * kSlots + j);
+      const uint32_t id = __float_as_uint(p.w);
+      if (id == kEmptyId) continue;
+      const unsigned long long k = key64(sqdist3(qx, qy, qz, p.x, p.y, p.z), id);
+      if (k < best) {
+        best = k;
+        bref = b * kSlots + j;
+      }
+    }
+  }
+}
+
+__device__ void far_search_warp(const MapView& m, float qx, float qy, float qz, unsigned long long& okey, uint32_t& oref) {
+  const int lane = threadIdx.x & 31;
+  const float h = m.cell_size, hb = 4.f * m.cell_size;
+  const int cx = vox_of(qx, m.ds) >> m.cell_shift, cy = vox_of(qy, m.ds) >> m.cell_shift, cz = vox_of(qz, m.ds) >> m.cell_shift;
+  const int bx = cx >> 2, by = cy >> 2, bz = cz >> 2;
+  // distance from q to the nearest face of its own block
+  const float fx = qx - (float)bx * hb, fy = qy - (float)by * hb, fz = qz - (float)bz * hb;
+  const float edge = fmaxf(fminf(fminf(fminf(fx, fy), fz), fminf(fminf(hb - fx, hb - fy), hb - fz)), 0.f);
+  unsigned long long best = ~0ull;
+  uint32_t bref = kNone;
+  bool found_in_rings = false;
+  for (int ring = 0; ring <= kFarRings; ++ring) {
+    if (ring >= 1 && best != ~0ull) {  // everything within `reach` of q lies in the cube of rings < ring
+      const float reach = ((float)(ring - 1) * hb + edge) * 0.9999f;
+      if (__uint_as_float((uint32_t)(best >> 32)) < reach * reach) {
+        found_in_rings = true;
+        break;
+      }
+    }
+    const int side = 2 * ring + 1, total = side * side * side;
+    for (int idx = lane; idx < total; idx += 32) {
+      const int dz = idx / (side * side) - ring, dy = (idx / side) % side - ring, dx = idx % side - ring;
+      if (max(max(abs(dx), abs(dy)), abs(dz)) != ring) continue;
+      const int ox = bx + dx, oy = by + dy, oz = bz + dz;
+      unsigned long long word = __ldg(m.occ + occ_word_of(m, ox, oy, oz));
+      while (word) {
+        const int b = __ffsll((long long)word) - 1;
+        word &= word - 1;
+        const int ccx = ox * 4 + (b & 3), ccy = oy * 4 + ((b >> 2) & 3), ccz = oz * 4 + (b >> 4);
+        const float bd = cell_box_d2(qx, qy, qz, ccx, ccy, ccz, h) * 0.9999f;
+        if (best != ~0ull && bd > __uint_as_float((uint32_t)(best >> 32))) continue;
+        far_scan_cell(m, ccx, ccy, ccz, qx, qy, qz, best, bref);
+      }
+    }
+    // the warp's best so far, in every lane (tightens the pruning of the next shell)
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+      const unsigned long long ok = __shfl_xor_sync(0xFFFFFFFFu, best, off);
+      const uint32_t orf = __shfl_xor_sync(0xFFFFFFFFu, bref, off);
+      if (ok < best) {
+        best = ok;
+        bref = orf;
+      }
+    }
+    if (ring == kFarRings && best != ~0ull) {
+      const float reach = ((float)ring * hb + edge) * 0.9999f;
+      found_in_rings = __uint_as_float((uint32_t)(best >> 32)) < reach * reach;
+    }
+  }
+  if (!found_in_rings) {  // nothing (provably nearest) within the shells: every bucket handed out so far
+    const uint32_t top = min(m.ctr->pool_top, m.pool_cap);
+    const size_t total = (size_t)top * kSlots;
+    for (size_t i = lane; i < total; i += 32) {
+      const float4 p = __ldg(m.slots + i);
+      const uint32_t id = __float_as_uint(p.w);
+      if (id == kEmptyId) continue;
+      const unsigned long long k = key64(sqdist3(qx, qy, qz, p.x, p.y, p.z), id);
+      if (k < best) {
+        best = k;
+        bref = (uint32_t)i;
+      }
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+      const unsigned long long ok = __shfl_xor_sync(0xFFFFFFFFu, best, off);
+      const uint32_t orf = __shfl_xor_sync(0xFFFFFFFFu, bref, off);
+      if (ok < best) {
+        best = ok;
+        bref = orf;
+      }
+    }
+  }
+  okey = best;
+  oref = bref;
+}
+
 }  // namespace lio

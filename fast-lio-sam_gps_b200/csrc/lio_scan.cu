@@ -25,7 +25,8 @@ constexpr int kMaxVals = 92;  // 12 cols: 78 + 12 + 2
 template <int G>
 __global__ void __launch_bounds__(kKnnBlock) k_scan_knn(MapView m, const float4* __restrict__ body, int n, StateArg st, float max_d2,
                                                         float4* __restrict__ nn, float* __restrict__ nn_d2,
-                                                        int* __restrict__ nn_cnt) {
+                                                        int* __restrict__ nn_cnt, double* __restrict__ knn_state) {
+  if (knn_state && blockIdx.x == 0 && threadIdx.x < 36) knn_state[threadIdx.x] = st.s[threadIdx.x];
   const Group<G> g;
   const int groups_per_block = kKnnBlock / G;
   const int gid = blockIdx.x * groups_per_block + (threadIdx.x / G);
@@ -287,11 +288,13 @@ __global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, cons
                                                                float* __restrict__ nn_d2, int* __restrict__ nn_cnt, TileQueue* __restrict__ q,
                                                                unsigned long long* __restrict__ queue, uint32_t qcap,
                                                                uint32_t* __restrict__ left, const IekfCtl* __restrict__ ctl,
-                                                               uint32_t* __restrict__ stats, uint4* __restrict__ prof_out, uint32_t prof_cap) {
+                                                               uint32_t* __restrict__ stats, uint4* __restrict__ prof_out, uint32_t prof_cap,
+                                                               double* __restrict__ knn_state) {
   __shared__ TileSmem smem[kTileWarps];
   __shared__ StateArg s_st;
   if (DEV && (ctl->finished || !ctl->converge)) return;  // cached neighbours are reused (ekfom_data.converge == false)
   const StateArg& st = block_state<DEV>(st_param, ctl, s_st);
+  if (XFORM && knn_state && blockIdx.x == 0 && threadIdx.x < 36) knn_state[threadIdx.x] = st.s[threadIdx.x];  // for k_far_nn (map_incremental)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned lt = (1u << lane) - 1u;
   TileSmem& sm = smem[warp];
@@ -661,10 +664,10 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
     }
     const unsigned vmask = __ballot_sync(0xFFFFFFFFu, valid);
     if (vmask) {
-      if (valid) {
+      // every lane stages its row (all zeros when the point is not selected: fma(0, 0, sum) == sum exactly), so the pair sums
+      // run over a fixed 32 rows in ascending order - no bit scan, no data-dependent trip count
 #pragma unroll
-        for (int j = 0; j < NC; ++j) s_rows[warp][lane][j] = row[j];
-      }
+      for (int j = 0; j < NC; ++j) s_rows[warp][lane][j] = row[j];
       __syncwarp();
 #pragma unroll
       for (int j = 0; j < VPL; ++j) {
@@ -672,12 +675,8 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
         if (v < NV) {
           const int a = s_pa[v], b = s_pb[v];
           double sum = acc[j];
-          unsigned mm = vmask;
-          while (mm) {
-            const int r = __ffs(mm) - 1;
-            mm &= mm - 1;
-            sum = fma(s_rows[warp][r][a], s_rows[warp][r][b], sum);
-          }
+#pragma unroll 8
+          for (int r = 0; r < 32; ++r) sum = fma(s_rows[warp][r][a], s_rows[warp][r][b], sum);
           acc[j] = sum;
         }
       }
@@ -715,7 +714,7 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
   for (int v = lane; v < NV; v += 32) {
     const int nb = gridDim.x;
     double sum = 0.0;
-    constexpr int U = 8;
+    constexpr int U = 16;
     for (int b0 = warp; b0 < nb; b0 += kRedWarps * U) {
       double t[U];
 #pragma unroll
@@ -763,6 +762,38 @@ __global__ void __launch_bounds__(kRedBlock, (NCOL == 6) ? 4 : 2) k_plane_reduce
   }
 }
 
+// ---------------------------------------------------------------- far nearest neighbour (map_incremental's points_near[0])
+// For the scan points whose search found nothing within max_sqdist: their unbounded nearest map point, searched from the
+// world position they had at the LAST search (knn_state), as upstream's cached Nearest_Points[i][0] was.  far[i].w = id bits,
+// 0xFFFFFFFF: none.  A warp takes 32 consecutive points and serves the (few) flagged ones one after the other.
+__global__ void __launch_bounds__(128) k_far_nn(MapView m, const float4* __restrict__ body, int n, const double* __restrict__ knn_state,
+                                                const int* __restrict__ nn_cnt, float4* __restrict__ far, const int* __restrict__ n_ptr) {
+  if (n_ptr) n = *n_ptr;
+  __shared__ StateArg s_st;
+  if (threadIdx.x < 36) s_st.s[threadIdx.x] = knn_state[threadIdx.x];
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool want = i < n && nn_cnt[i] == 0;
+  float qx = 0.f, qy = 0.f, qz = 0.f;
+  if (want) {
+    const float4 b = __ldg(body + i);
+    body_to_world(s_st, b.x, b.y, b.z, qx, qy, qz);
+  }
+  unsigned todo = __ballot_sync(0xFFFFFFFFu, want);
+  float4 mine = make_float4(0.f, 0.f, 0.f, __uint_as_float(kEmptyId));
+  while (todo) {
+    const int src = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const float x = __shfl_sync(0xFFFFFFFFu, qx, src), y = __shfl_sync(0xFFFFFFFFu, qy, src), z = __shfl_sync(0xFFFFFFFFu, qz, src);
+    unsigned long long key;
+    uint32_t ref;
+    far_search_warp(m, x, y, z, key, ref);
+    if (lane == src && key != ~0ull) mine = __ldg(m.slots + ref);
+  }
+  if (i < n) far[i] = mine;
+}
+
 // ---------------------------------------------------------------- map_incremental (device side)
 // class per point: 0 skip, 1 PointToAdd, 2 PointNoNeedDownsample; block counts for the ordered compaction
 template <bool DEV>
@@ -770,7 +801,7 @@ __global__ void __launch_bounds__(256) k_classify(const float4* __restrict__ bod
                                                   const int* __restrict__ nn_cnt, int flg_ekf_inited, float fs, MapCounters* ctr,
                                                   float4* __restrict__ world, uint8_t* __restrict__ cls,
                                                   uint32_t* __restrict__ blk_cnt, const IekfCtl* __restrict__ ctl,
-                                                  const int* __restrict__ n_ptr) {
+                                                  const int* __restrict__ n_ptr, const float4* __restrict__ far) {
   if (n_ptr) n = *n_ptr;  // graph form: the grid covers the padded size, the true size sits in device memory
   __shared__ uint32_t s_cnt[2];
   __shared__ StateArg s_st;
@@ -786,11 +817,15 @@ __global__ void __launch_bounds__(256) k_classify(const float4* __restrict__ bod
     world[i] = make_float4(wx, wy, wz, 0.f);
     const int cnt = nn_cnt[i];
     c = 1;
-    if (cnt > 0 && flg_ekf_inited) {
+    // points_near[0]: the nearest of the cached neighbours, or - when the search found none within max_sqdist - the far
+    // nearest map point upstream's unbounded search would have cached (k_far_nn); none at all: PointToAdd
+    float4 n0 = make_float4(0.f, 0.f, 0.f, __uint_as_float(kEmptyId));
+    if (cnt > 0) n0 = __ldg(nn + (size_t)i * kK);
+    else if (far) n0 = __ldg(far + i);
+    if (__float_as_uint(n0.w) != kEmptyId && flg_ekf_inited) {
       const float mx = floorf(wx / fs) * fs + 0.5f * fs, my = floorf(wy / fs) * fs + 0.5f * fs,
                   mz = floorf(wz / fs) * fs + 0.5f * fs;
       const float dist = sqdist3(wx, wy, wz, mx, my, mz);
-      const float4 n0 = __ldg(nn + (size_t)i * kK);
       if (fabsf(n0.x - mx) > 0.5f * fs && fabsf(n0.y - my) > 0.5f * fs && fabsf(n0.z - mz) > 0.5f * fs) {
         c = 2;
       } else if (ctr->live >= kK) {
@@ -979,6 +1014,9 @@ int scan_alloc(lio_ctx* c) {
   LIO_CUDA(cudaMalloc(&c->sel, n));
   LIO_CUDA(cudaMalloc(&c->plane, sizeof(float4) * n));
   LIO_CUDA(cudaMalloc(&c->pfit, sizeof(float4) * n));
+  LIO_CUDA(cudaMalloc(&c->far_nn, sizeof(float4) * n));
+  LIO_CUDA(cudaMalloc(&c->knn_state_dev, sizeof(double) * 36));
+  LIO_CUDA(cudaMemsetAsync(c->knn_state_dev, 0, sizeof(double) * 36, c->stream));
   LIO_CUDA(cudaMalloc(&c->cls, n));
   LIO_CUDA(cudaMalloc(&c->blk_cnt, sizeof(uint32_t) * 2 * ((n + 255) / 256 + 1)));
   LIO_CUDA(cudaMalloc(&c->list_add, sizeof(float4) * n));
@@ -1049,6 +1087,8 @@ void scan_free(lio_ctx* c) {
   cudaFree(c->sel);
   cudaFree(c->plane);
   cudaFree(c->pfit);
+  cudaFree(c->far_nn);
+  cudaFree(c->knn_state_dev);
   cudaFree(c->rows);
   cudaFree(c->cls);
   cudaFree(c->blk_cnt);
@@ -1216,13 +1256,23 @@ int tile_tasks_of_last_search(lio_ctx* c, uint32_t* n_tasks) {
 int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
   const int n = c->scan_n;
   const StateArg st = make_state(state_host);
-  if (c->knn_mode == 1 && (!c->order_valid || c->resort_each_search)) {  // LIO_RESORT=0: once per scan (later calls move the points by centimetres)
+  // The curve order is recomputed when the state has moved enough since the last ordering for queries to change cells
+  // (> 2 cm or > 1 mrad: 5 cm at 50 m); between the searches of a scan that is the size of the IEKF correction.
+  bool moved = true;
+  if (c->order_valid && c->resort_each_search) {
+    double dp = 0.0, dr = 0.0;
+    for (int k = 0; k < 3; ++k) dp = std::max(dp, std::fabs(state_host[k] - c->sort_state[k]));
+    for (int k = 3; k < 21; ++k) dr = std::max(dr, std::fabs(state_host[k] - c->sort_state[k]));  // rot, offset_R (entries), offset_T
+    moved = dp > 0.02 || dr > 0.001;
+  }
+  if (c->knn_mode == 1 && (!c->order_valid || (c->resort_each_search && moved))) {  // LIO_RESORT=0: once per scan
     timer_begin(c, T_SORT);
     int rc = c->sort_graph_ok ? tile_order_graph(c, n, state_host) : LIO_E_STATE;
     if (rc == LIO_E_STATE && !c->sort_graph_ok) rc = tile_order(c, c->body, n, st, true);
     timer_end(c);
     if (rc) return rc;
     c->order_valid = true;
+    std::memcpy(c->sort_state, state_host, sizeof(c->sort_state));
   }
   timer_begin(c, T_KNN);
   if (c->knn_mode == 1) {
@@ -1235,19 +1285,19 @@ int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
     if (dev_loop) {
       k_knn_tile<true, true><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->tile_sorted, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
                                                                                   c->nn, nullptr, c->nn_cnt, ctr, c->tile_queue, qcap, c->tile_vals[0],
-                                                                                  c->iekf_ctl, c->tile_stats, c->tile_prof, c->tile_prof_cap);
+                                                                                  c->iekf_ctl, c->tile_stats, c->tile_prof, c->tile_prof_cap, c->knn_state_dev);
       k_knn_left<true, true><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
                                                                          nullptr, c->nn_cnt, ctr, ctr_next, c->tile_stats, c->iekf_ctl);
     } else {
       k_knn_tile<true, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->tile_sorted, c->tile_vals[1], n, st, kK, c->cfg.max_sqdist,
                                                                                    c->nn, nullptr, c->nn_cnt, ctr, c->tile_queue, qcap, c->tile_vals[0],
-                                                                                   nullptr, c->tile_stats, c->tile_prof, c->tile_prof_cap);
+                                                                                   nullptr, c->tile_stats, c->tile_prof, c->tile_prof_cap, c->knn_state_dev);
       k_knn_left<true, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, c->body, c->tile_vals[0], st, kK, c->cfg.max_sqdist, c->nn,
                                                                           nullptr, c->nn_cnt, ctr, ctr_next, c->tile_stats, nullptr);
     }
     c->launches += 1;
   } else {
-    k_scan_knn<8><<<knn_grid(c, n, 8), kKnnBlock, 0, c->stream>>>(c->map, c->body, n, st, c->cfg.max_sqdist, c->nn, c->nn_d2, c->nn_cnt);
+    k_scan_knn<8><<<knn_grid(c, n, 8), kKnnBlock, 0, c->stream>>>(c->map, c->body, n, st, c->cfg.max_sqdist, c->nn, c->nn_d2, c->nn_cnt, c->knn_state_dev);
   }
   c->launches += 1;
   timer_end(c);
@@ -1257,21 +1307,24 @@ int scan_knn(lio_ctx* c, const double* state_host, bool dev_loop) {
 }
 
 int knn_batch(lio_ctx* c, const float4* q_dev, int n, int k, float max_d2, float4* out_nn, float* out_d2, int* out_cnt) {
+  if (c->knn_mode == 1) {
+    StateArg st{};
+    timer_begin(c, T_SORT);
+    int rc = tile_order(c, q_dev, n, st, false);
+    timer_end(c);
+    if (rc) return rc;
+    c->order_valid = false;  // the scan's order lived in the same buffers
+  }
   timer_begin(c, T_KNN);
   if (c->knn_mode == 1) {
-    const bool keep = c->order_valid && (uint32_t)n <= c->tile_cap;  // the scan's order lives in the same buffers
     StateArg st{};
-    int rc = tile_order(c, q_dev, n, st, false);
-    if (rc) return rc;
-    (void)keep;
-    c->order_valid = false;
     TileQueue* sets = reinterpret_cast<TileQueue*>(c->tile_stats + 4);
     TileQueue* ctr = sets + (c->tile_flip & 1);
     TileQueue* ctr_next = sets + ((c->tile_flip + 1) & 1);
     c->tile_flip ^= 1;
     k_knn_tile<false, false><<<tile_grid(c, n), kTileWarps * 32, 0, c->stream>>>(c->map, c->tile_sorted, c->tile_vals[1], n, st, k, max_d2, out_nn,
                                                                                   out_d2, out_cnt, ctr, c->tile_queue, 2 * c->tile_cap, c->tile_vals[0],
-                                                                                  nullptr, c->tile_stats, nullptr, 0u);
+                                                                                  nullptr, c->tile_stats, nullptr, 0u, nullptr);
     if (c->batch_left_warp)
       k_knn_left<false, false><<<c->n_sms * kLeftGridMult, kKnnBlock, 0, c->stream>>>(c->map, q_dev, c->tile_vals[0], st, k, max_d2, out_nn, out_d2, out_cnt,
                                                                          ctr, ctr_next, c->tile_stats, nullptr);
@@ -1347,14 +1400,15 @@ static int classify_insert_graph(lio_ctx* c, const double* state_host, int flg_e
     LIO_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeRelaxed));
     cudaMemcpyAsync(c->map_args_dev, c->map_args_host, sizeof(KeysArgs), cudaMemcpyHostToDevice, c->stream);
     StateArg unused{};
+    k_far_nn<<<(n_pad + 127) / 128, 128, 0, c->stream>>>(c->map, c->body, n_pad, c->knn_state_dev, c->nn_cnt, c->far_nn, n_ptr);
     k_classify<true><<<blocks, 256, 0, c->stream>>>(c->body, n_pad, unused, c->nn, c->nn_cnt, flg_ekf_inited, c->cfg.filter_size_map,
-                                                    c->map.ctr, c->world, c->cls, c->blk_cnt, st_view, n_ptr);
+                                                    c->map.ctr, c->world, c->cls, c->blk_cnt, st_view, n_ptr, c->far_nn);
     k_scan_blocks<<<1, 1024, 0, c->stream>>>(c->blk_cnt, blocks, c->map.ctr);
     k_scatter_lists<<<blocks, 256, 0, c->stream>>>(c->world, c->cls, n_pad, c->blk_cnt, c->list_add, c->list_nodown, n_ptr);
     const int64_t l0 = c->launches;
     int r1 = map_add_device(c, c->list_add, (uint32_t)n_pad, &c->map.ctr->list_add, true);
     int r2 = map_add_device(c, c->list_nodown, (uint32_t)n_pad, &c->map.ctr->list_nodown, false);
-    c->map_graph_launches = 3 + (int)(c->launches - l0);
+    c->map_graph_launches = 4 + (int)(c->launches - l0);
     c->launches = l0;
     const cudaError_t ce = cudaStreamEndCapture(c->stream, &graph);
     c->timing = was_timing;
@@ -1387,17 +1441,18 @@ int scan_classify_insert(lio_ctx* c, const double* state_host, int flg_ekf_inite
   }
   const int blocks = (n + 255) / 256;
   timer_begin(c, T_CLASSIFY);
+  k_far_nn<<<(n + 127) / 128, 128, 0, c->stream>>>(c->map, c->body, n, c->knn_state_dev, c->nn_cnt, c->far_nn, nullptr);
   if (dev_loop) {
     StateArg unused{};
     k_classify<true><<<blocks, 256, 0, c->stream>>>(c->body, n, unused, c->nn, c->nn_cnt, flg_ekf_inited, c->cfg.filter_size_map, c->map.ctr,
-                                                    c->world, c->cls, c->blk_cnt, c->iekf_ctl, nullptr);
+                                                    c->world, c->cls, c->blk_cnt, c->iekf_ctl, nullptr, c->far_nn);
   } else {
     k_classify<false><<<blocks, 256, 0, c->stream>>>(c->body, n, make_state(state_host), c->nn, c->nn_cnt, flg_ekf_inited,
-                                                     c->cfg.filter_size_map, c->map.ctr, c->world, c->cls, c->blk_cnt, nullptr, nullptr);
+                                                     c->cfg.filter_size_map, c->map.ctr, c->world, c->cls, c->blk_cnt, nullptr, nullptr, c->far_nn);
   }
   k_scan_blocks<<<1, 1024, 0, c->stream>>>(c->blk_cnt, blocks, c->map.ctr);
   k_scatter_lists<<<blocks, 256, 0, c->stream>>>(c->world, c->cls, n, c->blk_cnt, c->list_add, c->list_nodown, nullptr);
-  c->launches += 3;
+  c->launches += 4;
   timer_end(c);
   LIO_CUDA(cudaGetLastError());
   int rc = map_add_device(c, c->list_add, (uint32_t)n, &c->map.ctr->list_add, true);

@@ -70,6 +70,61 @@ static int copy_cloud_out(loop_ctx* c, uint32_t off, uint32_t n, float* out, int
   return LOOP_OK;
 }
 
+// General 4x4 inverse by cofactors in f64 (what `pose_eig_.inverse()` of pose_pcd.hpp:38 asks Eigen for; Eigen's fixed-size
+// 4x4 path is a cofactor expansion too, its exact operation order is not in the mount: [RECALL]).  Row-major in, row-major out.
+static bool inv4(const double* m, double* o) {
+  // 2x2 minors of rows (0,1) and rows (2,3); adjugate entries are sums of three minor products; same operation order as the
+  // oracle's restatement so that the re-expressed clouds compare bit for bit
+  const double a0 = m[0] * m[5] - m[4] * m[1], a1 = m[0] * m[6] - m[4] * m[2], a2 = m[0] * m[7] - m[4] * m[3];
+  const double a3 = m[1] * m[6] - m[5] * m[2], a4 = m[1] * m[7] - m[5] * m[3], a5 = m[2] * m[7] - m[6] * m[3];
+  const double b5 = m[10] * m[15] - m[14] * m[11], b4 = m[9] * m[15] - m[13] * m[11], b3 = m[9] * m[14] - m[13] * m[10];
+  const double b2 = m[8] * m[15] - m[12] * m[11], b1 = m[8] * m[14] - m[12] * m[10], b0 = m[8] * m[13] - m[12] * m[9];
+  const double det = a0 * b5 - a1 * b4 + a2 * b3 + a3 * b2 - a4 * b1 + a5 * b0;
+  if (det == 0.0 || !std::isfinite(det)) return false;
+  const double r = 1.0 / det;
+  const double adj[16] = {
+      m[5] * b5 - m[6] * b4 + m[7] * b3,    -m[1] * b5 + m[2] * b4 - m[3] * b3,  m[13] * a5 - m[14] * a4 + m[15] * a3,  -m[9] * a5 + m[10] * a4 - m[11] * a3,
+      -m[4] * b5 + m[6] * b2 - m[7] * b1,   m[0] * b5 - m[2] * b2 + m[3] * b1,   -m[12] * a5 + m[14] * a2 - m[15] * a1, m[8] * a5 - m[10] * a2 + m[11] * a1,
+      m[4] * b4 - m[5] * b2 + m[7] * b0,    -m[0] * b4 + m[1] * b2 - m[3] * b0,  m[12] * a4 - m[13] * a2 + m[15] * a0,  -m[8] * a4 + m[9] * a2 - m[11] * a0,
+      -m[4] * b3 + m[5] * b1 - m[6] * b0,   m[0] * b3 - m[1] * b1 + m[2] * b0,   -m[12] * a3 + m[13] * a1 - m[14] * a0, m[8] * a3 - m[9] * a1 + m[10] * a0};
+  for (int i = 0; i < 16; ++i) o[i] = adj[i] * r;
+  return true;
+}
+
+// fetchClosestKeyframeIdx (loop_closure.cpp:18-40) for many query keyframes at once: one warp per query strides over the
+// candidates [0, K-2]; the winner is the smallest (distance, index) among those within `radius` and older than `time_diff`,
+// i.e. the first minimum of the reference's ascending scan.  pos = x y z stamp per keyframe.
+__global__ void __launch_bounds__(256) k_fetch_closest(const double* __restrict__ pos, int K, const int* __restrict__ query, int n_query,
+                                                       double radius, double time_diff, int* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w >= n_query) return;
+  const int q = query[w];
+  double best = radius * 3.0;
+  int bi = -1;
+  if (q >= 0 && q < K) {
+    const double qx = pos[4 * q], qy = pos[4 * q + 1], qz = pos[4 * q + 2], qt = pos[4 * q + 3];
+    for (int i = lane; i + 1 < K; i += 32) {
+      const double dx = pos[4 * i] - qx, dy = pos[4 * i + 1] - qy, dz = pos[4 * i + 2] - qz;
+      const double d = sqrt(dx * dx + dy * dy + dz * dz);
+      if (radius > d && time_diff < (qt - pos[4 * i + 3]) && d < best) {  // (ascending i per lane: the first minimum is kept)
+        best = d;
+        bi = i;
+      }
+    }
+  }
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const double ob = __shfl_xor_sync(0xFFFFFFFFu, best, off);
+    const int oi = __shfl_xor_sync(0xFFFFFFFFu, bi, off);
+    if (oi >= 0 && (bi < 0 || ob < best || (ob == best && oi < bi))) {
+      best = ob;
+      bi = oi;
+    }
+  }
+  if (lane == 0) out[w] = bi;
+}
+
 }  // namespace loopb
 
 using namespace loopb;
@@ -147,6 +202,7 @@ void loop_ctx_destroy(loop_ctx* c) {
   c->blk2job.release(); c->cub_tmp.release(); c->vox.release(); c->trees.release(); c->tree_pts.release();
   c->nodes.release(); c->pairs.release(); c->cur.release(); c->match.release(); c->md2.release(); c->blk2pair.release();
   if (c->active_host) cudaFreeHost(c->active_host);
+  c->kf_pos_dev.release(); c->gtab.release(); c->gnext.release();
   if (c->active_dev) cudaFree(c->active_dev);
   if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
   delete c;
@@ -173,6 +229,7 @@ int loop_keyframe_add(loop_ctx* c, const float* xyzi, int n, const double* pose1
   c->kf_n.push_back((uint32_t)n);
   c->kf_pose.insert(c->kf_pose.end(), pose16, pose16 + 16);
   c->kf_stamp.push_back(stamp);
+  c->kf_pos_dirty = true;
   c->kf_used += (size_t)n;
   if (idx_out) *idx_out = (int)c->kf_n.size() - 1;
   return LOOP_OK;
@@ -184,6 +241,45 @@ int loop_keyframe_set_pose(loop_ctx* c, int idx, const double* pose16) {
     return LOOP_E_ARG;
   }
   std::memcpy(&c->kf_pose[16 * (size_t)idx], pose16, sizeof(double) * 16);
+  c->kf_pos_dirty = true;
+  return LOOP_OK;
+}
+
+// PosePcd's constructor (pose_pcd.hpp:25-43): the cloud arrives in the WORLD frame (FAST-LIO publishes /cloud_registered
+// there) and is kept in the LiDAR frame, pcd_ = transformPcd(tmp, pose_eig_.inverse()).  The re-expression runs on the
+// device, on the copy that has just landed in the store: no host pass over the points, no second H2D.
+int loop_keyframe_add_world(loop_ctx* c, const float* xyzi_world, int n, const double* pose16, double stamp, int* idx_out) {
+  int rc = check(c);
+  if (rc) return rc;
+  if (!pose16) {
+    lio::set_error("loop_keyframe_add_world: null pose");
+    return LOOP_E_ARG;
+  }
+  double inv[16];
+  if (!inv4(pose16, inv)) {
+    lio::set_error("loop_keyframe_add_world: singular pose");
+    return LOOP_E_ARG;
+  }
+  const size_t off = c->kf_used;
+  int idx = -1;
+  if ((rc = loop_keyframe_add(c, xyzi_world, n, pose16, stamp, &idx))) return rc;
+  if ((rc = transform_store_inplace(c, off, n, inv))) return rc;
+  if (idx_out) *idx_out = idx;
+  return LOOP_OK;
+}
+
+int loop_keyframe_set_poses(loop_ctx* c, const int* idx, const double* pose16s, int n) {
+  if (!c || n < 0 || (n > 0 && (!idx || !pose16s))) {
+    lio::set_error("loop_keyframe_set_poses: bad arguments");
+    return LOOP_E_ARG;
+  }
+  for (int k = 0; k < n; ++k)
+    if (idx[k] < 0 || idx[k] >= (int)c->kf_n.size()) {
+      lio::set_error("loop_keyframe_set_poses: bad index %d", idx[k]);
+      return LOOP_E_ARG;
+    }
+  for (int k = 0; k < n; ++k) std::memcpy(&c->kf_pose[16 * (size_t)idx[k]], pose16s + 16 * (size_t)k, sizeof(double) * 16);
+  if (n) c->kf_pos_dirty = true;
   return LOOP_OK;
 }
 
@@ -195,6 +291,7 @@ int loop_keyframe_clear(loop_ctx* c) {
   c->kf_n.clear();
   c->kf_pose.clear();
   c->kf_stamp.clear();
+  c->kf_pos_dirty = true;
   c->kf_used = 0;
   return LOOP_OK;
 }
@@ -220,6 +317,47 @@ int loop_fetch_closest(loop_ctx* c, int query_idx, double radius, double time_di
     }
   }
   *closest_out = best;
+  return LOOP_OK;
+}
+
+// the same for n queries in one launch (every keyframe of a tick, or all of them when the pose graph is re-checked): the
+// translations and stamps live on the device and are refreshed only after keyframes were added or poses changed
+int loop_fetch_closest_batch(loop_ctx* c, const int* query_idx, int n, double radius, double time_diff, int* closest_out) {
+  int rc = check(c);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!query_idx || !closest_out))) {
+    lio::set_error("loop_fetch_closest_batch: bad arguments");
+    return LOOP_E_ARG;
+  }
+  const int K = (int)c->kf_n.size();
+  for (int k = 0; k < n; ++k)
+    if (query_idx[k] < 0 || query_idx[k] >= K) {
+      lio::set_error("loop_fetch_closest_batch: bad query index %d", query_idx[k]);
+      return LOOP_E_ARG;
+    }
+  if (n == 0) return LOOP_OK;
+  cudaStream_t s = c->stream;
+  if (c->kf_pos_dirty) {
+    std::vector<double> pos(4 * (size_t)K);
+    for (int i = 0; i < K; ++i) {
+      const double* p = &c->kf_pose[16 * (size_t)i];
+      pos[4 * i] = p[3], pos[4 * i + 1] = p[7], pos[4 * i + 2] = p[11], pos[4 * i + 3] = c->kf_stamp[i];
+    }
+    if ((rc = c->kf_pos_dev.ensure(std::max<size_t>(pos.size(), 4)))) return rc;
+    LOOP_CUDA(cudaMemcpyAsync(c->kf_pos_dev.p, pos.data(), sizeof(double) * pos.size(), cudaMemcpyHostToDevice, s));
+    LOOP_CUDA(cudaStreamSynchronize(s));  // `pos` is a host temporary
+    c->kf_pos_dirty = false;
+  }
+  // queries in, answers out: the tail of the 32-bit scratch buffers
+  if ((rc = c->vals_a.ensure((size_t)n)) || (rc = c->vals_b.ensure((size_t)n))) return rc;
+  int* q_dev = reinterpret_cast<int*>(c->vals_a.p);
+  int* o_dev = reinterpret_cast<int*>(c->vals_b.p);
+  LOOP_CUDA(cudaMemcpyAsync(q_dev, query_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, s));
+  k_fetch_closest<<<(n * 32 + 255) / 256, 256, 0, s>>>(c->kf_pos_dev.p, K, q_dev, n, radius, time_diff, o_dev);
+  c->launches += 1;
+  LOOP_CUDA(cudaGetLastError());
+  LOOP_CUDA(cudaMemcpyAsync(closest_out, o_dev, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
+  LOOP_CUDA(cudaStreamSynchronize(s));
   return LOOP_OK;
 }
 

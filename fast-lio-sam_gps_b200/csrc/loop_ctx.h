@@ -143,6 +143,8 @@ struct loop_ctx {
   std::vector<uint32_t> kf_off, kf_n;
   std::vector<double> kf_pose;  // 16 per keyframe
   std::vector<double> kf_stamp;
+  loopb::DevBuf<double> kf_pos_dev;   // x y z stamp per keyframe, for loop_fetch_closest_batch (refreshed when kf_pos_dirty)
+  bool kf_pos_dirty = true;
 
   // voxelisation workspace
   loopb::DevBuf<loopb::SegDev> segs;
@@ -201,6 +203,7 @@ struct JobHost {
 int voxelize_jobs(loop_ctx* c, const std::vector<JobHost>& jobs_host, float leaf);
 int voxelize_host_cloud(loop_ctx* c, const float* xyzi, int n, float leaf);
 int transform_host_cloud(loop_ctx* c, const float* xyzi, int n, const double* T16, float* out);
+int transform_store_inplace(loop_ctx* c, size_t off, int n, const double* T16);  // keyframe store points [off, off + n) <- T * p
 // loads explicit clouds as "already voxelised" jobs (loop_icp_align)
 int load_clouds(loop_ctx* c, const float* const* clouds, const int* ns, int n_clouds);
 

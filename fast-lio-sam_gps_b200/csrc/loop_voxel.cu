@@ -361,6 +361,37 @@ static int voxelize_raw(loop_ctx* c, const std::vector<JobDev>& jd, const SegDev
   return LOOP_OK;
 }
 
+namespace {
+// pts[i] = T * pts[i] in place, the arithmetic of k_submap (f64 matrix applied to f32 points, transformPcd / pcl::transformPointCloud
+// with a Matrix4d): the keyframe constructor's re-expression of the published world-frame cloud in the LiDAR frame
+struct Mat34 {
+  double T[12];
+};
+__global__ void __launch_bounds__(256) k_transform_inplace(float4* __restrict__ pts, uint32_t n, Mat34 m) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = pts[i];
+  const double x = p.x, y = p.y, z = p.z;
+  const double* T = m.T;
+  float4 o;
+  o.x = (float)(((T[0] * x + T[1] * y) + T[2] * z) + T[3]);
+  o.y = (float)(((T[4] * x + T[5] * y) + T[6] * z) + T[7]);
+  o.z = (float)(((T[8] * x + T[9] * y) + T[10] * z) + T[11]);
+  o.w = p.w;
+  pts[i] = o;
+}
+}  // namespace
+
+int transform_store_inplace(loop_ctx* c, size_t off, int n, const double* T16) {
+  if (n <= 0) return LOOP_OK;
+  Mat34 m;
+  std::memcpy(m.T, T16, sizeof(double) * 12);
+  k_transform_inplace<<<grid_of((size_t)n, 256), 256, 0, c->stream>>>(c->kf_pts.p + off, (uint32_t)n, m);
+  c->launches += 1;
+  LOOP_CUDA(cudaGetLastError());
+  return LOOP_OK;
+}
+
 int voxelize_jobs(loop_ctx* c, const std::vector<JobHost>& jobs_host, float leaf) {
   std::vector<JobDev> jd;
   std::vector<SegDev> sd;

@@ -57,6 +57,9 @@ LOOP_SYMBOLS = {
     "loop_last_error": (C.c_char_p, []),
     "loop_keyframe_add": (C.c_int, [C.c_void_p, _f32p, C.c_int, _f64p, C.c_double, _i32p]),
     "loop_keyframe_set_pose": (C.c_int, [C.c_void_p, C.c_int, _f64p]),
+    "loop_keyframe_add_world": (C.c_int, [C.c_void_p, _f32p, C.c_int, _f64p, C.c_double, _i32p]),
+    "loop_keyframe_set_poses": (C.c_int, [C.c_void_p, _i32p, _f64p, C.c_int]),
+    "loop_fetch_closest_batch": (C.c_int, [C.c_void_p, _i32p, C.c_int, C.c_double, C.c_double, _i32p]),
     "loop_keyframe_count": (C.c_int, [C.c_void_p]),
     "loop_keyframe_clear": (C.c_int, [C.c_void_p]),
     "loop_fetch_closest": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_double, _i32p]),
@@ -164,6 +167,29 @@ class LoopClosure:
         idx = C.c_int(-1)
         self._check(self.lib.loop_keyframe_add(self.h, _p(xyzi, _f32p), len(xyzi), _p(pose, _f64p), float(stamp), C.byref(idx)))
         return idx.value
+
+    def add_keyframe_world(self, xyzi_world, pose, stamp=0.0):
+        """PosePcd's constructor (pose_pcd.hpp:25-43): world-frame cloud in, LiDAR-frame cloud stored (pose^-1 on the device)."""
+        xyzi = _f32(xyzi_world).reshape(-1, 4)
+        pose = _f64(pose).reshape(16)
+        idx = C.c_int(-1)
+        self._check(self.lib.loop_keyframe_add_world(self.h, _p(xyzi, _f32p), len(xyzi), _p(pose, _f64p), float(stamp), C.byref(idx)))
+        return idx.value
+
+    def set_poses(self, idx, poses_corrected):
+        """pose_corrected_eig_ of several keyframes at once (after a pose-graph update)."""
+        idx = np.ascontiguousarray(idx, np.int32).reshape(-1)
+        poses = _f64(poses_corrected).reshape(-1, 16)
+        assert len(idx) == len(poses)
+        self._check(self.lib.loop_keyframe_set_poses(self.h, _p(idx, _i32p), _p(poses, _f64p), len(idx)))
+
+    def fetch_closest_keyframe_idx_batch(self, query_idx):
+        """fetchClosestKeyframeIdx for many query keyframes in one device launch."""
+        q = np.ascontiguousarray(query_idx, np.int32).reshape(-1)
+        out = np.full(len(q), -1, np.int32)
+        self._check(self.lib.loop_fetch_closest_batch(self.h, _p(q, _i32p), len(q), self.loop_detection_radius,
+                                                      self.loop_detection_timediff_threshold, _p(out, _i32p)))
+        return out
 
     def set_pose(self, idx, pose_corrected):
         pose = _f64(pose_corrected).reshape(16)

@@ -126,7 +126,10 @@ def raycast(scene, origin, dirs, max_range=120.0, min_range=0.5):
             tf = np.nanmin(np.maximum(t0, t1), axis=1)
             ok = (tf >= tn) & (tn > min_range)
             t = np.where(ok & (tn < t), tn, t)
-    for cy in scene["cyls"]:
+    cyls = scene["cyls"]
+    if len(cyls):  # a cylinder whose axis is farther than max_range + r cannot be hit within max_range (hits beyond are dropped below)
+        cyls = cyls[np.hypot(cyls[:, 0] - o[0], cyls[:, 1] - o[1]) - cyls[:, 2] < max_range]
+    for cy in cyls:
         cx, cyy, r, h = cy
         ox, oy = o[0] - cx, o[1] - cyy
         a = d[:, 0] ** 2 + d[:, 1] ** 2

@@ -84,7 +84,10 @@ int lio_map_knn(lio_ctx* ctx, const float* q_xyz, int n, int k, float max_sqdist
                 int* cnt);
 
 /* ---- scan + measurement model: replaces h_share_model -------------------------------------------- */
-/* feats_down_body: n points (xyz, stride 3 floats, HOST memory) -> device. Invalidates cached neighbours. */
+/* feats_down_body: n points (xyz, stride 3 floats, HOST memory) -> device. Invalidates cached neighbours.
+ * The copy is ASYNCHRONOUS on the context's stream: a pageable buffer has been staged by the time the call returns, but a
+ * PINNED buffer is still being read by the device afterwards - keep it unchanged until the next call that waits for the
+ * stream (lio_h_share, lio_iekf_update*, lio_ctx_sync) has returned. */
 int lio_scan_upload(lio_ctx* ctx, const float* body_xyz, int n);
 /* Optional: start the host->device copy of the NEXT scan on a separate copy stream so that it overlaps the kernels of the
  * scan in flight (the LiDAR driver hands over scan i+1 while scan i is in the filter).  A following lio_scan_upload with
@@ -113,10 +116,13 @@ int lio_iekf_update(lio_ctx* ctx, double* state, double* P, double R, int max_it
                     double* iter_states, int* n_eff_trace, int* knn_trace, int* iters_done);
 /* The per-scan body of the reference's main loop in one call: update_iterated_dyn_share_modified followed
  * by map_incremental() at the updated state (laserMapping.cpp main loop: `kf.update_iterated_dyn_share_modified(...)`
- * ... `map_incremental()`; absent submodule).  Everything — the measurement-model calls, the 23x23
- * update of every iteration and the map update — is enqueued on the device without a host round trip; the
- * call returns when the updated (state, P) have landed in host memory (the map insert may still be in flight
- * on the context's stream). */
+ * ... `map_incremental()`; absent submodule).  By default the iterations run as a HOST loop: one
+ * measurement-model launch per iteration, the 156 doubles of H^T H / H^T z read from mapped pinned memory (a ~10 us poll), the
+ * 23x23 update on the host (measured faster than the device form: 0.53 vs 0.79 ms per scan).  LIO_IEKF_MODE=device in the
+ * environment at context creation enqueues the whole loop - measurement calls, the 23x23 update of every iteration and the map
+ * update - without a host round trip.  Either way the call returns when the updated (state, P) are in host memory; the map
+ * insert may still be in flight on the context's stream, and a capacity error it runs into is reported by the NEXT
+ * lio_iekf_update* / lio_map_add / lio_ctx_sync call (LIO_E_CAPACITY). */
 int lio_iekf_update_map(lio_ctx* ctx, double* state, double* P, double R, int max_iter, const double* limit,
                         int flg_ekf_inited, double* iter_states, int* n_eff_trace, int* knn_trace, int* iters_done);
 
@@ -136,7 +142,9 @@ int lio_scan_get_body(lio_ctx* ctx, float* body_xyz);
 
 /* map_incremental() at the final state, entirely on the device (classification from the cached
  * neighbours, then Add_Points(PointToAdd,true) and Add_Points(PointNoNeedDownsample,false)).
- * Counts are optional; asking for them synchronises. */
+ * points_near[0] of a point whose search found nothing within max_sqdist is its FAR nearest map point (upstream's search is
+ * unbounded; looked up here, from the point's position at the last search); a scan that was never searched has empty
+ * Nearest_Points and every point goes to PointToAdd.  Counts are optional; asking for them synchronises. */
 int lio_map_incremental(lio_ctx* ctx, const double* state, int flg_ekf_inited, int* n_add, int* n_nodown);
 /* lasermap_fov_segment(): slides the local-map cube around pos_lid[3]; boxes_out optional (3x6 floats). */
 int lio_fov_segment(lio_ctx* ctx, const double* pos_lid, float* boxes_out, int* n_boxes);

@@ -10,6 +10,8 @@
  *   fast_lio_sam/include/utilities.hpp:158-171 voxelizePcd                            -> loop_voxelize
  *   fast_lio_sam/include/pose_pcd.hpp:7-19     PosePcd (pcd_ in the LiDAR frame, pose_corrected_eig_, timestamp_)
  *                                                                                     -> loop_keyframe_add / _set_pose
+ *   fast_lio_sam/include/pose_pcd.hpp:25-43    PosePcd constructor (world-frame cloud -> LiDAR frame by pose^-1)
+ *                                                                                     -> loop_keyframe_add_world
  *   fast_lio_sam/include/loop_closure.h:31-37  RegistrationOutput                     -> loop_result
  *   fast_lio_sam/include/loop_closure.h:21-29  LoopClosureConfig                      -> loop_config
  * The PCL 1.10 arithmetic behind those calls (VoxelGrid, IterativeClosestPoint, TransformationEstimationSVD,
@@ -75,13 +77,27 @@ const char* loop_last_error(void);
 /* Appends a keyframe: pcd_ (n points, LiDAR frame), pose_corrected_eig_ (16 doubles), timestamp_.  Returns its index
  * in *idx_out (optional).  The cloud is copied to the device once and stays resident. */
 int loop_keyframe_add(loop_ctx* ctx, const float* xyzi, int n, const double* pose16, double stamp, int* idx_out);
+/* PosePcd's constructor (pose_pcd.hpp:25-43): the cloud is the WORLD-frame cloud FAST-LIO publishes; the store keeps
+ * pcd_ = transformPcd(cloud, pose.inverse()) (pose_pcd.hpp:38-39).  The re-expression runs on the device on the uploaded
+ * copy.  pose16 = pose_eig_ (= pose_corrected_eig_ at construction).  Fails with LOOP_E_ARG on a singular pose. */
+int loop_keyframe_add_world(loop_ctx* ctx, const float* xyzi_world, int n, const double* pose16, double stamp, int* idx_out);
 /* pose_corrected_eig_ = ... (fast_lio_sam.cpp pose-graph corrections) */
 int loop_keyframe_set_pose(loop_ctx* ctx, int idx, const double* pose16);
+/* the same for n keyframes in one call (idx[n], pose16s[16 n]): what a caller sends after a pose-graph update - only the
+ * poses that changed, not all of them */
+int loop_keyframe_set_poses(loop_ctx* ctx, const int* idx, const double* pose16s, int n);
 int loop_keyframe_count(loop_ctx* ctx);
 int loop_keyframe_clear(loop_ctx* ctx);
 
-/* fetchClosestKeyframeIdx: nearest keyframe among [0, size-2] within `radius` and older than `time_diff`; -1 if none. */
+/* fetchClosestKeyframeIdx: nearest keyframe among [0, size-2] within `radius` and older than `time_diff`; -1 if none.
+ * The query's pose and stamp are those stored under query_idx, and the answer is the POSITION of the keyframe in the store;
+ * the reference returns keyframes[idx].idx_ and reads the pose of the PosePcd it is handed (loop_closure.cpp:18-40) - the
+ * same thing as long as idx_ equals the position and the query is the stored keyframe, which is how fast_lio_sam.cpp:684-698
+ * uses it. */
 int loop_fetch_closest(loop_ctx* ctx, int query_idx, double radius, double time_diff, int* closest_out);
+/* the same for n query keyframes in one device launch (closest_out[n]); translations and stamps are kept on the device and
+ * re-sent only after keyframes were added or poses changed */
+int loop_fetch_closest_batch(loop_ctx* ctx, const int* query_idx, int n, double radius, double time_diff, int* closest_out);
 
 /* ---- utilities.hpp ---------------------------------------------------------------------------------------------------- */
 /* transformPcd: out[i] = T * in[i] (f64 matrix applied to f32 points), intensity copied. */

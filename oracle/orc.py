@@ -76,9 +76,12 @@ def lib():
         L.orc_loop_destroy.argtypes = [C.c_void_p]
         L.orc_loop_add_keyframe.restype = C.c_int
         L.orc_loop_add_keyframe.argtypes = [C.c_void_p, _f32p, C.c_int, _f64p, C.c_double]
+        L.orc_loop_set_pose.argtypes = [C.c_void_p, C.c_int, _f64p]
         L.orc_loop_fetch_closest.restype = C.c_int
         L.orc_loop_fetch_closest.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double]
         L.orc_transform_pcd.argtypes = [_f32p, C.c_int, _f64p, _f32p]
+        L.orc_pose_inverse.restype = C.c_int
+        L.orc_pose_inverse.argtypes = [_f64p, _f64p]
         L.orc_voxelize.restype = C.c_int
         L.orc_voxelize.argtypes = [_f32p, C.c_int, C.c_float, _f32p]
         L.orc_loop_set_src_dst.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, _f32p, _i32p, _f32p, _i32p, C.c_int]
@@ -281,6 +284,10 @@ class OracleLoop:
         pose = _f64(pose).reshape(16)
         return self.L.orc_loop_add_keyframe(self.h, _p(xyzi, _f32p), len(xyzi), _p(pose, _f64p), stamp)
 
+    def set_pose(self, idx, pose):
+        pose = _f64(pose).reshape(16)
+        self.L.orc_loop_set_pose(self.h, int(idx), _p(pose, _f64p))
+
     def fetch_closest(self, query_idx, radius, tdiff):
         return self.L.orc_loop_fetch_closest(self.h, query_idx, radius, tdiff)
 
@@ -323,6 +330,20 @@ def transform_pcd(xyzi, T):
     out = np.zeros_like(xyzi)
     lib().orc_transform_pcd(_p(xyzi, _f32p), len(xyzi), _p(T, _f64p), _p(out, _f32p))
     return out
+
+
+def pose_inverse(T):
+    """pose_eig_.inverse() of the PosePcd constructor (pose_pcd.hpp:38)."""
+    T = _f64(T).reshape(16)
+    out = np.zeros(16)
+    if not lib().orc_pose_inverse(_p(T, _f64p), _p(out, _f64p)):
+        raise ValueError("singular pose")
+    return out.reshape(4, 4)
+
+
+def keyframe_from_world(xyzi_world, pose):
+    """PosePcd constructor: pcd_ = transformPcd(cloud_world, pose.inverse()) (pose_pcd.hpp:37-39)."""
+    return transform_pcd(xyzi_world, pose_inverse(pose))
 
 
 def voxelize(xyzi, leaf):

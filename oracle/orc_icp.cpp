@@ -483,6 +483,12 @@ int orc_loop_add_keyframe(void* h, const float* xyzi, int n, const double* pose1
   return (int)L->kfs.size() - 1;
 }
 
+// pose_corrected_eig_ = ... after a pose-graph update
+void orc_loop_set_pose(void* h, int idx, const double* pose16) {
+  LoopOracle* L = (LoopOracle*)h;
+  std::memcpy(L->kfs[idx].pose, pose16, sizeof(L->kfs[idx].pose));
+}
+
 // loop_closure.cpp:18-40
 int orc_loop_fetch_closest(void* h, int query_idx, double radius, double tdiff) {
   LoopOracle* L = (LoopOracle*)h;
@@ -498,6 +504,37 @@ int orc_loop_fetch_closest(void* h, int query_idx, double radius, double tdiff) 
     }
   }
   return best;
+}
+
+// pose_eig_.inverse() of the PosePcd constructor (/root/reference/fast_lio_sam/include/pose_pcd.hpp:38): Eigen's fixed-size
+// 4x4 inverse is a cofactor expansion [RECALL: Eigen/src/LU/InverseImpl.h, not in the mount]; restated here as adjugate /
+// determinant in f64, laid out by 2x2 minors.  Returns 0 for a singular matrix.
+int orc_pose_inverse(const double* m, double* o) {
+  // minors of the lower and the upper two rows
+  const double s0 = m[0] * m[5] - m[4] * m[1], s1 = m[0] * m[6] - m[4] * m[2], s2 = m[0] * m[7] - m[4] * m[3];
+  const double s3 = m[1] * m[6] - m[5] * m[2], s4 = m[1] * m[7] - m[5] * m[3], s5 = m[2] * m[7] - m[6] * m[3];
+  const double c5 = m[10] * m[15] - m[14] * m[11], c4 = m[9] * m[15] - m[13] * m[11], c3 = m[9] * m[14] - m[13] * m[10];
+  const double c2 = m[8] * m[15] - m[12] * m[11], c1 = m[8] * m[14] - m[12] * m[10], c0 = m[8] * m[13] - m[12] * m[9];
+  const double det = s0 * c5 - s1 * c4 + s2 * c3 + s3 * c2 - s4 * c1 + s5 * c0;
+  if (det == 0.0 || !std::isfinite(det)) return 0;
+  const double r = 1.0 / det;
+  o[0] = (m[5] * c5 - m[6] * c4 + m[7] * c3) * r;
+  o[1] = (-m[1] * c5 + m[2] * c4 - m[3] * c3) * r;
+  o[2] = (m[13] * s5 - m[14] * s4 + m[15] * s3) * r;
+  o[3] = (-m[9] * s5 + m[10] * s4 - m[11] * s3) * r;
+  o[4] = (-m[4] * c5 + m[6] * c2 - m[7] * c1) * r;
+  o[5] = (m[0] * c5 - m[2] * c2 + m[3] * c1) * r;
+  o[6] = (-m[12] * s5 + m[14] * s2 - m[15] * s1) * r;
+  o[7] = (m[8] * s5 - m[10] * s2 + m[11] * s1) * r;
+  o[8] = (m[4] * c4 - m[5] * c2 + m[7] * c0) * r;
+  o[9] = (-m[0] * c4 + m[1] * c2 - m[3] * c0) * r;
+  o[10] = (m[12] * s4 - m[13] * s2 + m[15] * s0) * r;
+  o[11] = (-m[8] * s4 + m[9] * s2 - m[11] * s0) * r;
+  o[12] = (-m[4] * c3 + m[5] * c1 - m[6] * c0) * r;
+  o[13] = (m[0] * c3 - m[1] * c1 + m[2] * c0) * r;
+  o[14] = (-m[12] * s3 + m[13] * s1 - m[14] * s0) * r;
+  o[15] = (m[8] * s3 - m[9] * s1 + m[10] * s0) * r;
+  return 1;
 }
 
 void orc_transform_pcd(const float* in, int n, const double* T, float* out) {

@@ -17,6 +17,7 @@
 // kNN sets and plane-validity masks can be compared bit-exactly.
 #include <cstdint>
 #include <cstdio>
+#include <cstring>
 #include <cfloat>
 #include <cmath>
 #include <vector>
@@ -169,6 +170,10 @@ struct Scan {
   std::vector<int> nn_cnt;    // n
   std::vector<uint8_t> sel;   // point_selected_surf
   std::vector<float> plane;   // n x 4: a b c pd2
+  // Nearest_Points[i][0] of the points whose 5-NN search found nothing within max_d2: upstream's search is unbounded, so the
+  // cached list still starts with the (far) nearest map point, and map_incremental looks at it.  far[i] = xyz + id bits,
+  // id 0xFFFFFFFF: none (empty map, or no search ran for this scan)
+  std::vector<float> far;     // n x 4
 };
 
 struct Ctx {
@@ -200,6 +205,18 @@ int h_share_model(Ctx& c, const St& s, bool converge, double* HTH, double* HTz, 
       KnnHit hits[kK];
       int cnt = c.map.knn(pw, kK, c.max_d2, hits);
       sc.nn_cnt[i] = cnt;
+      {
+        float* f = &sc.far[size_t(i) * 4];
+        uint32_t none = 0xFFFFFFFFu;
+        std::memcpy(&f[3], &none, 4);
+        if (cnt == 0) {  // the unbounded search's first neighbour (only map_incremental reads it)
+          KnnHit far_hit[1];
+          if (c.map.knn(pw, 1, INFINITY, far_hit) == 1) {
+            f[0] = far_hit[0].x; f[1] = far_hit[0].y; f[2] = far_hit[0].z;
+            std::memcpy(&f[3], &far_hit[0].id, 4);
+          }
+        }
+      }
       for (int k = 0; k < cnt; ++k) {
         float* d = &sc.nn[(size_t(i) * kK + k) * 4];
         d[0] = hits[k].x; d[1] = hits[k].y; d[2] = hits[k].z;
@@ -446,21 +463,28 @@ void map_incremental(Ctx& c, const St& s, int flg_ekf_inited, int* n_add, int* n
   for (int i = 0; i < sc.n; ++i) {
     float* pw = &sc.world[3 * i];
     body_to_world(s, &sc.body[3 * i], pw);
-    // With a bounded search (max_d2 = 5 >= (fs*sqrt3)^2) an empty cache means "all neighbours far":
-    // the reference would take a branch that ends in an add either way.
-    if (sc.nn_cnt[i] > 0 && flg_ekf_inited) {
+    // Upstream: `if (!Nearest_Points[i].empty() && flg_EKF_inited)`.  Its search is unbounded, so the cached list is empty
+    // only when no search ran (or the map was empty); a point with no neighbour within max_d2 still has its far nearest
+    // neighbour at the head of the list (sc.far), which decides between the two lists like any other points_near[0].
+    const float* n0 = nullptr;
+    if (sc.nn_cnt[i] > 0) n0 = &sc.nn[size_t(i) * kK * 4];
+    else {
+      uint32_t fid;
+      std::memcpy(&fid, &sc.far[size_t(i) * 4 + 3], 4);
+      if (fid != 0xFFFFFFFFu) n0 = &sc.far[size_t(i) * 4];
+    }
+    if (n0 && flg_ekf_inited) {
       float mid[3];
       for (int a = 0; a < 3; ++a) mid[a] = std::floor(pw[a] / fs) * fs + 0.5f * fs;
       float dist = sqdist3(pw[0], pw[1], pw[2], mid[0], mid[1], mid[2]);
-      const float* n0 = &sc.nn[size_t(i) * kK * 4];
       if (std::fabs(n0[0] - mid[0]) > 0.5f * fs && std::fabs(n0[1] - mid[1]) > 0.5f * fs && std::fabs(n0[2] - mid[2]) > 0.5f * fs) {
         no_down.insert(no_down.end(), pw, pw + 3);
         continue;
       }
       bool need_add = true;
-      // reference breaks out when points_near.size() < 5, which with an unbounded search only happens
-      // when the whole map holds < 5 points; bounded-search neighbours beyond max_d2 can never be
-      // closer to the voxel centre than the point itself, so scanning the found ones is equivalent.
+      // reference breaks out when points_near.size() < 5, which with an unbounded search only happens when the whole map
+      // holds < 5 points; neighbours beyond max_d2 can never be closer to the voxel centre than the point itself, so
+      // scanning the ones found within max_d2 is equivalent.
       if (c.map.size() >= kK) {
         for (int k = 0; k < sc.nn_cnt[i]; ++k) {
           const float* q = &sc.nn[(size_t(i) * kK + k) * 4];
@@ -581,6 +605,11 @@ void orc_scan_set(void* h, const float* body_xyz, int n) {
   s.nn_cnt.assign(n, 0);
   s.sel.assign(n, 0);
   s.plane.assign(size_t(n) * 4, 0.f);
+  s.far.assign(size_t(n) * 4, 0.f);
+  for (int i = 0; i < n; ++i) {  // no search has run for this scan: no far neighbour either
+    const uint32_t none = 0xFFFFFFFFu;
+    std::memcpy(&s.far[size_t(i) * 4 + 3], &none, 4);
+  }
 }
 
 int orc_h_share(void* h, const double* state36, int converge, double* HTH, double* HTz, double* res_sum,

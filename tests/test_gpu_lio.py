@@ -488,6 +488,42 @@ def test_map_capacity_error_is_loud_and_harmless(pkg, synth, monkeypatch):
     g.close()
 
 
+def test_map_incremental_far_neighbour_parity(pkg, orc, synth):
+    """k_far_nn: the scan points whose search finds nothing within max_sqdist are classified with their unbounded nearest map
+    point, through the occupancy shells (3-20 m away) and through the full-pool scan (> 32 m): list sizes and the live map
+    bit-identical to the oracle, in both launch forms; no search for the scan -> every point is a PointToAdd."""
+    from test_oracle_lio import _far_world
+
+    m, scan = _far_world()
+    st = synth.make_state(np.eye(3), np.zeros(3))
+    for graph in ("1", "0"):
+        os.environ["LIO_MAP_GRAPH"] = graph
+        g = pkg.LioContext(0.5, max_points=1 << 16, max_scan=4096)
+        o = orc.OracleLio(0.5)
+        g.map_build(m)
+        o.map_build(m)
+        g.scan_upload(scan)
+        o.scan_upload(scan)
+        g.h_share(st, True)
+        o.h_share(st, True)
+        assert np.array_equal(g.scan_get()["nn_cnt"], o.scan_get()["nn_cnt"])
+        got, ref = g.map_incremental(st, True), o.map_incremental(st, True)
+        assert got == ref and got[1] > 0
+        gx, gi = g.map_export()
+        ox, oi = o.map_export()
+        assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
+        # a scan that was never searched: Nearest_Points is empty for every point
+        g.scan_upload(scan + np.float32(0.11))
+        o.scan_upload(scan + np.float32(0.11))
+        got, ref = g.map_incremental(st, True), o.map_incremental(st, True)
+        assert got == ref and got[1] == 0
+        gx, gi = g.map_export()
+        ox, oi = o.map_export()
+        assert np.array_equal(gi, oi) and np.array_equal(gx, ox)
+        g.close()
+    os.environ.pop("LIO_MAP_GRAPH", None)
+
+
 def _predict(state, dR, dt):
     """state (+) body-frame motion (dR, dt): pos += rot*dt, rot = rot*dR  (state layout of include/lio_b200.h)."""
     s = state.copy()

@@ -53,6 +53,66 @@ def test_transform_pcd_bit_exact(closers, orc, synth, drive):
     assert len(g.transform_pcd(np.zeros((0, 4), np.float32), T)) == 0
 
 
+def test_keyframe_add_world_bit_exact(loop_mod, orc, synth, drive):
+    """loop_keyframe_add_world = PosePcd's constructor on the device (pose_pcd.hpp:37-39): the stored cloud equals
+    transformPcd(cloud_world, pose.inverse()) of the oracle bit for bit, and a submap built from such keyframes equals the one
+    built from keyframes ingested in the LiDAR frame by the oracle's constructor."""
+    clouds, est, _, stamps = drive
+    g = loop_mod.LoopClosure(num_submap_keyframes=2)
+    o = orc.OracleLoop(max_corr_dist=g.icp_max_corr_dist, nthreads=0)
+    for k in range(8):
+        world = orc.transform_pcd(clouds[k], est[k])  # what FAST-LIO publishes on /cloud_registered
+        assert g.add_keyframe_world(world, est[k], stamps[k]) == k
+        o.add_keyframe(orc.keyframe_from_world(world, est[k]), est[k], stamps[k])
+    assert np.abs(orc.pose_inverse(est[3]) - np.linalg.inv(np.asarray(est[3], np.float64))).max() < 1e-12
+    gs, gd = g.set_src_and_dst_cloud(5, 2, 2, 0.3)
+    os_, od = o.set_src_dst(5, 2, 2, 0.3)
+    assert np.array_equal(gs, os_) and np.array_equal(gd, od)
+    with pytest.raises(Exception):
+        g.add_keyframe_world(clouds[0], np.zeros((4, 4)), 0.0)  # singular pose
+    g.close()
+
+
+def test_fetch_closest_batch_matches(closers, drive):
+    """loop_fetch_closest_batch (one device launch) = loop_fetch_closest per query = the reference's scan
+    (loop_closure.cpp:18-40), before and after a bulk pose update (loop_keyframe_set_poses)."""
+    g, o = closers
+    K = len(drive[0])
+    q = np.arange(K, dtype=np.int32)
+    stamps = np.asarray(drive[3], np.float64)
+    keep = g.loop_detection_timediff_threshold
+    g.loop_detection_timediff_threshold = 0.25 * float(stamps[-1] - stamps[0])  # so that the return pass finds the outbound one
+    try:
+        _fetch_closest_checks(g, o, drive, K, q)
+    finally:
+        g.loop_detection_timediff_threshold = keep
+
+
+def _fetch_closest_checks(g, o, drive, K, q):
+    one = np.array([g.fetch_closest_keyframe_idx(int(i)) for i in q], np.int32)
+    assert np.array_equal(g.fetch_closest_keyframe_idx_batch(q), one)
+    assert np.array_equal(one, np.array([o.fetch_closest(int(i), g.loop_detection_radius, g.loop_detection_timediff_threshold) for i in q]))
+    assert (one >= 0).any() and (one < 0).any()
+    # move a few poses (as a pose-graph update does), only those are re-sent
+    est = [np.asarray(e, np.float64).reshape(4, 4).copy() for e in drive[1]]
+    idx = np.array([1, 4, K - 3], np.int32)
+    moved = []
+    for i in idx:
+        T = est[i].copy()
+        T[:3, 3] += [0.7, -0.4, 0.1]
+        moved.append(T)
+    g.set_poses(idx, np.array(moved))
+    for i, T in zip(idx, moved):
+        o.set_pose(int(i), T)
+    again = g.fetch_closest_keyframe_idx_batch(q)
+    assert np.array_equal(again, np.array([g.fetch_closest_keyframe_idx(int(i)) for i in q], np.int32))
+    assert np.array_equal(again, np.array([o.fetch_closest(int(i), g.loop_detection_radius, g.loop_detection_timediff_threshold) for i in q]))
+    g.set_poses(idx, np.array([est[i] for i in idx]))  # restore for the tests that follow
+    for i in idx:
+        o.set_pose(int(i), est[i])
+    assert len(g.fetch_closest_keyframe_idx_batch(np.zeros(0, np.int32))) == 0
+
+
 def test_pose_pcd_ctor_stores_lidar_frame(closers, orc, synth, drive):
     """pose_pcd.hpp:38-39: the published world-frame cloud is re-expressed in the LiDAR frame with pose^-1; and the loop
     factor built from a verified pair (fast_lio_sam.cpp:699-717) closes the chain pose_from * measured = pose_to."""
@@ -247,3 +307,23 @@ def test_errors(loop_mod, pkg):
     g.close()
     with pytest.raises(pkg.LioError):
         loop_mod.LoopClosure(max_iterations=0)
+
+
+def test_pool_equals_single_context(loop_mod, closers, drive):
+    """LoopClosurePool: a batch cut into contiguous parts verified concurrently by several contexts gives the results of one
+    context, pair for pair (candidate pairs are independent, loop_closure.cpp:101-126)."""
+    g, _ = closers
+    clouds, est, _, stamps = drive
+    K = len(clouds)
+    pairs = [(K - 2 - i, 1 + (i % 4)) for i in range(7)]
+    ref = g.verify_batch(pairs)
+    for n_ctx in (2, 3):
+        pool = loop_mod.LoopClosurePool(n_ctx, num_submap_keyframes=g.num_submap_keyframes)
+        for c, e, s in zip(clouds, est, stamps):
+            pool.add_keyframe(c, e, s)
+        assert [hi - lo for lo, hi in pool.split(len(pairs))] == [len(range(*loop_mod.shard_pairs(len(pairs), k, n_ctx))) for k in range(n_ctx)]
+        got = pool.verify_batch(pairs)
+        assert len(got) == len(ref)
+        for a, b in zip(got, ref):
+            same_result(a, b)
+        pool.close()

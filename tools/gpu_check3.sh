@@ -10,7 +10,7 @@ print('value', d['value'], 'e2e', d['e2e']['value'], 'wall', d.get('e2e_wall',{}
 print({k: round(v['mean_ms'],4) for k,v in d['kernel_ms'].items()}, d['knn_deferred_fraction'])
 print('parity', d.get('parity_at_config')); print('cpu', d.get('cpu_baseline'))
 PY
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/launches_dbg.csv python bench.py --no-loop --no-parity --no-cpu-baseline --steps 3 --warmup 3 > gpurun_out/ncu_dbg.log 2>&1; echo "ncu exit $?"
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/launches_dbg.csv python bench.py --no-loop --no-configs --no-parity --no-cpu-baseline --steps 3 --warmup 3 > gpurun_out/ncu_dbg.log 2>&1; echo "ncu exit $?"
 python - <<'PY'
 import csv, collections
 rows=[r for r in csv.reader(open('gpurun_out/launches_dbg.csv')) if len(r)>5]

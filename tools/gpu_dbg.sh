@@ -1,7 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
 timeout 900 python tools/map_diff.py > gpurun_out/map_diff.log 2>&1; echo "map_diff exit $?"; tail -40 gpurun_out/map_diff.log
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/launches_dbg.csv python bench.py --no-loop --no-parity --no-cpu-baseline --steps 3 --warmup 3 > gpurun_out/ncu_dbg.log 2>&1; echo "ncu exit $?"
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/launches_dbg.csv python bench.py --no-loop --no-configs --no-parity --no-cpu-baseline --steps 3 --warmup 3 > gpurun_out/ncu_dbg.log 2>&1; echo "ncu exit $?"
 python - <<'PY'
 import csv, collections
 rows=[r for r in csv.reader(open('gpurun_out/launches_dbg.csv')) if len(r)>5]
