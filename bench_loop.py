@@ -109,22 +109,30 @@ def gpu_loop(loop_mod, w, pairs, device=0, steps=5, warmup=1, stream=None, e2e_s
     # context) -> loop_verify_batch -> results back in host memory; host wall clock with a device synchronise on both sides
     clouds = [np.ascontiguousarray(c, np.float32) for c in w["clouds"]]
     e2e_s = []
+    # (ONE context here: every context needs its own copy of the store, and from host memory the second upload costs more
+    # than the overlap of two contexts wins back)
+    pool.close()
+    pool = loop_mod.LoopClosurePool(1, **kw)
+    arrays1 = pool.make_arrays(pairs)
+    for c, e, s in zip(clouds, w["est"], w["stamps"]):
+        pool.add_keyframe(c, e, s)
+    pool.verify_arrays(arrays1)  # (untimed: workspace growth)
     for _ in range(e2e_steps):
         pool.clear()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for c, e, s in zip(clouds, w["est"], w["stamps"]):
             pool.add_keyframe(c, e, s)
-        pool.verify_arrays(arrays)
+        pool.verify_arrays(arrays1)
         torch.cuda.synchronize()
         e2e_s.append(time.perf_counter() - t0)
     e2e = None
     if e2e_s:
-        again = [loop_mod._result(r[i]) for a, k, r in arrays for i in range(k)]
+        again = [loop_mod._result(r[i]) for a, k, r in arrays1 for i in range(k)]
         same = all(x["score"] == y["score"] and np.array_equal(x["T"], y["T"]) for x, y in zip(again, out))
-        e2e = {"seconds_per_batch": float(np.mean(e2e_s)), "h2d_bytes_per_step": int(len(pool.ctx) * (sum(c.nbytes for c in clouds) + 17 * 8 * len(clouds)) + 8 * n),
+        e2e = {"seconds_per_batch": float(np.mean(e2e_s)), "h2d_bytes_per_step": int(sum(c.nbytes for c in clouds) + 17 * 8 * len(clouds) + 8 * n),
                "d2h_bytes_per_step": int(C.sizeof(loop_mod.LoopResult) * n), "same_results_as_resident_store": bool(same), "batches": len(e2e_s),
-               "contexts": len(pool.ctx), "same_results_as_one_context": bool(same_split)}
+               "contexts": 1, "same_results_as_one_context": bool(same_split)}
     pool.close()
     return out, ms, kt, stats, launches, e2e
 

@@ -7,13 +7,14 @@ import subprocess
 import sys
 
 KEYS = [
-    ("gpu__time_duration.sum", "duration", "us", 1.0),
+    ("gpu__time_duration.sum", "duration", "", 1.0),
     ("launch__grid_size", "grid", "", 1.0),
     ("launch__block_size", "block", "", 1.0),
     ("launch__registers_per_thread", "registers/thread", "", 1.0),
-    ("sm__warps_active.avg.pct_of_peak_sustained_active", "sm__warps_active", "% of peak", 1.0),
-    ("smsp__issue_active.avg.pct", "smsp__issue_active", "%", 1.0),
+    ("sm__warps_active.avg.pct_of_peak_sustained_active", "sm__warps_active", "% of peak (while active)", 1.0),
     ("smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__issue_active", "% (while active)", 1.0),
+    ("sm__issue_active.avg.pct_of_peak_sustained_elapsed", "sm__issue_active", "% (of elapsed)", 1.0),
+    ("dram__throughput.avg.pct_of_peak_sustained_elapsed", "dram throughput", "% of peak", 1.0),
     ("smsp__inst_executed.sum", "warp instructions", "", 1.0),
     ("smsp__thread_inst_executed_per_inst_executed.ratio", "active threads / instruction", "", 1.0),
     ("dram__bytes_read.sum", "dram read", "", 1.0),
