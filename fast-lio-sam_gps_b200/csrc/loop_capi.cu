@@ -160,6 +160,7 @@ int loop_ctx_create(const loop_config* cfg, loop_ctx** out) {
   c->cfg = *cfg;
   c->n_sms = prop.multiProcessorCount;
   if (const char* e = getenv("LOOP_TREE_ORDER")) c->tree_order = (e[0] == 'm' || e[0] == '0') ? 0 : 1;
+  if (const char* e = getenv("LOOP_TREE")) c->tree_kind = (e[0] == 'b' || e[0] == '0') ? 0 : 1;
   if (const char* e = getenv("LOOP_GRID")) c->use_grid = e[0] != '0';
   if (const char* e = getenv("LOOP_SAMPLE_FIRST")) c->sample_first = e[0] != '0';
   c->prm.max_d2 = cfg->max_corr_dist * cfg->max_corr_dist;
@@ -203,6 +204,7 @@ void loop_ctx_destroy(loop_ctx* c) {
   c->nodes.release(); c->pairs.release(); c->cur.release(); c->match.release(); c->md2.release(); c->blk2pair.release();
   if (c->active_host) cudaFreeHost(c->active_host);
   c->kf_pos_dev.release(); c->gtab.release(); c->gnext.release();
+  c->leaf_code.release(); c->leaf_parent.release(); c->node_parent.release(); c->node_flag.release();
   if (c->active_dev) cudaFree(c->active_dev);
   if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
   delete c;

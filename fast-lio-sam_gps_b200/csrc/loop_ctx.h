@@ -102,7 +102,8 @@ struct TreeDev {
   uint32_t src_off;   // the cloud's points in the voxelised buffer (original order)
   // uniform grid over the cloud (targets only): open-addressing table of (cell key -> first point of the cell), points of a
   // cell chained through gnext[] (indexed like the compact point space).  grid_mask == 0: no grid (the tree alone is used).
-  uint32_t grid_off, grid_mask, cmp_off, pad_;
+  uint32_t grid_off, grid_mask, cmp_off;
+  uint32_t lbvh;      // 1: the nodes form a radix tree over the leaves' curve keys (explicit child references), 0: implicit balanced tree
 };
 
 struct __align__(16) GCell {
@@ -162,6 +163,8 @@ struct loop_ctx {
   loopb::DevBuf<loopb::TreeDev> trees;
   loopb::DevBuf<float4> tree_pts;
   loopb::DevBuf<loopb::Node2> nodes;
+  loopb::DevBuf<uint32_t> leaf_code, leaf_parent, node_parent, node_flag;  // radix-tree build scratch (per leaf / per node of all trees)
+  int tree_kind = 1;                  // LOOP_TREE=balanced: implicit balanced tree (A/B); default: radix tree (LBVH)
   loopb::DevBuf<loopb::GCell> gtab;   // grids of the target clouds
   loopb::DevBuf<uint32_t> gnext;      // next point of the same cell (original index inside the cloud), 0xFFFFFFFF: end
   float grid_cell = 0.3f;             // cell edge of the target grids (the VoxelGrid leaf when the clouds come from it)
