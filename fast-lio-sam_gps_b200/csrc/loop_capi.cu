@@ -204,7 +204,7 @@ void loop_ctx_destroy(loop_ctx* c) {
   c->nodes.release(); c->pairs.release(); c->cur.release(); c->match.release(); c->md2.release(); c->blk2pair.release();
   if (c->active_host) cudaFreeHost(c->active_host);
   c->kf_pos_dev.release(); c->gtab.release(); c->gnext.release();
-  c->leaf_code.release(); c->leaf_parent.release(); c->node_parent.release(); c->node_flag.release();
+  c->leaf_code.release(); c->node_flag.release();
   if (c->active_dev) cudaFree(c->active_dev);
   if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
   delete c;

@@ -163,7 +163,7 @@ struct loop_ctx {
   loopb::DevBuf<loopb::TreeDev> trees;
   loopb::DevBuf<float4> tree_pts;
   loopb::DevBuf<loopb::Node2> nodes;
-  loopb::DevBuf<uint32_t> leaf_code, leaf_parent, node_parent, node_flag;  // radix-tree build scratch (per leaf / per node of all trees)
+  loopb::DevBuf<uint32_t> leaf_code, node_flag;  // radix-tree build scratch (curve key per leaf / fill state per node, all trees)
   int tree_kind = 1;                  // LOOP_TREE=balanced: implicit balanced tree (A/B); default: radix tree (LBVH)
   loopb::DevBuf<loopb::GCell> gtab;   // grids of the target clouds
   loopb::DevBuf<uint32_t> gnext;      // next point of the same cell (original index inside the cloud), 0xFFFFFFFF: end

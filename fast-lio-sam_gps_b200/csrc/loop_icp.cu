@@ -201,7 +201,6 @@ __device__ __forceinline__ int lbvh_delta(const uint32_t* __restrict__ code, int
 // one thread per internal node of every tree (tree t has nleaf - 1 of them, numbered from 0 = root)
 __global__ void __launch_bounds__(kBlock) k_lbvh_build(const TreeDev* __restrict__ trees, const uint32_t* __restrict__ pad_off, int n_trees,
                                                        uint32_t n_leaf_total, const uint32_t* __restrict__ leaf_code, Node2* __restrict__ nodes,
-                                                       uint32_t* __restrict__ leaf_parent, uint32_t* __restrict__ node_parent,
                                                        uint32_t* __restrict__ node_flag) {
   const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= n_leaf_total) return;
@@ -234,9 +233,6 @@ __global__ void __launch_bounds__(kBlock) k_lbvh_build(const TreeDev* __restrict
   Node2& nd = nodes[tr.node_off + i];
   nd.lo0.w = __uint_as_float(c0);
   nd.lo1.w = __uint_as_float(c1);
-  if (c0 & kLeafFlag) leaf_parent[leaf0 + gamma] = (uint32_t)i; else node_parent[tr.node_off + gamma] = (uint32_t)i;
-  if (c1 & kLeafFlag) leaf_parent[leaf0 + gamma + 1] = (uint32_t)i; else node_parent[tr.node_off + gamma + 1] = (uint32_t)i;
-  if (i == 0) node_parent[tr.node_off] = 0xFFFFFFFFu;
 }
 
 // Child boxes of every internal node, one block per tree, bottom-up in rounds: a node is filled in once both its children are
@@ -947,7 +943,6 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs, int n_tar
   if ((rc = c->trees.ensure(std::max(nt, 1))) || (rc = c->blk2job.ensure(offs.size())) || (rc = c->tree_pts.ensure(std::max<uint32_t>(pad, 1))) ||
       (rc = c->nodes.ensure(std::max<uint32_t>(node, 1))) || (rc = c->gtab.ensure(std::max<uint32_t>(gtot, 1))) ||
       (rc = c->gnext.ensure(std::max<uint32_t>(cmp, 1))) || (rc = c->leaf_code.ensure(pad / kLeafPts + 1)) ||
-      (rc = c->leaf_parent.ensure(pad / kLeafPts + 1)) || (rc = c->node_parent.ensure(std::max<uint32_t>(node, 1))) ||
       (rc = c->node_flag.ensure(std::max<uint32_t>(node, 1))))
     return rc;
   if (nt == 0) return LOOP_OK;
@@ -984,8 +979,7 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs, int n_tar
   }
   if (c->tree_kind && pad) {
     const uint32_t n_leaf_total = pad / kLeafPts;
-    k_lbvh_build<<<grid_of(n_leaf_total, kBlock), kBlock, 0, s>>>(c->trees.p, pad_off, nt, n_leaf_total, c->leaf_code.p, c->nodes.p, c->leaf_parent.p,
-                                                                   c->node_parent.p, c->node_flag.p);
+    k_lbvh_build<<<grid_of(n_leaf_total, kBlock), kBlock, 0, s>>>(c->trees.p, pad_off, nt, n_leaf_total, c->leaf_code.p, c->nodes.p, c->node_flag.p);
     k_lbvh_boxes<<<nt, 1024, 0, s>>>(c->trees.p, c->tree_pts.p, c->nodes.p, c->node_flag.p);
     c->launches += 2;
   } else {
