@@ -914,7 +914,7 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs, int n_tar
   cudaStream_t s = c->stream;
   c->trees_host.assign(nt, TreeDev{});
   std::vector<uint32_t> offs(2 * (size_t)nt + 2, 0);  // [0, nt): compact offsets, [nt, 2nt): padded offsets
-  uint32_t cmp = 0, pad = 0, node = 0, gtot = 0;
+  uint32_t cmp = 0, pad = 0, node = 0, gtot = 0, pad_targets = 0;  // pad_targets: padded points of the clouds that are searched
   for (int t = 0; t < nt; ++t) {
     const GridDev& g = c->grids_host[tree_jobs[t]];
     TreeDev& tr = c->trees_host[t];
@@ -938,6 +938,7 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs, int n_tar
     cmp += tr.n;
     pad += tr.nleaf * kLeafPts;
     node += tr.nleaf_pad;
+    if (t == n_targets - 1) pad_targets = pad;
   }
   int rc;
   if ((rc = c->trees.ensure(std::max(nt, 1))) || (rc = c->blk2job.ensure(offs.size())) || (rc = c->tree_pts.ensure(std::max<uint32_t>(pad, 1))) ||
@@ -977,13 +978,15 @@ static int build_trees(loop_ctx* c, const std::vector<int>& tree_jobs, int n_tar
                                                           c->leaf_code.p);
     c->launches += 1;
   }
-  if (c->tree_kind && pad) {
-    const uint32_t n_leaf_total = pad / kLeafPts;
-    k_lbvh_build<<<grid_of(n_leaf_total, kBlock), kBlock, 0, s>>>(c->trees.p, pad_off, nt, n_leaf_total, c->leaf_code.p, c->nodes.p, c->node_flag.p);
-    k_lbvh_boxes<<<nt, 1024, 0, s>>>(c->trees.p, c->tree_pts.p, c->nodes.p, c->node_flag.p);
+  // nodes only for the clouds that are searched: the targets come first in the list, the source clouds behind them went
+  // through the ordering pass for their curve order alone
+  if (c->tree_kind && pad_targets) {
+    const uint32_t n_leaf_total = pad_targets / kLeafPts;
+    k_lbvh_build<<<grid_of(n_leaf_total, kBlock), kBlock, 0, s>>>(c->trees.p, pad_off, n_targets, n_leaf_total, c->leaf_code.p, c->nodes.p, c->node_flag.p);
+    k_lbvh_boxes<<<n_targets, 1024, 0, s>>>(c->trees.p, c->tree_pts.p, c->nodes.p, c->node_flag.p);
     c->launches += 2;
-  } else {
-    k_tree_nodes<<<nt, 1024, 0, s>>>(c->trees.p, c->tree_pts.p, c->nodes.p);
+  } else if (n_targets > 0) {
+    k_tree_nodes<<<n_targets, 1024, 0, s>>>(c->trees.p, c->tree_pts.p, c->nodes.p);
     c->launches += 1;
   }
   tend(c);
