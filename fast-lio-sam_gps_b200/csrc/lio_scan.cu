@@ -265,6 +265,10 @@ __global__ void __launch_bounds__(256) k_sort_clear(SortScratch* __restrict__ sc
 }
 
 constexpr int kTileWarps = 4;
+#ifndef LIO_TILE_BLOCKS_PER_SM
+#define LIO_TILE_BLOCKS_PER_SM 8
+#endif
+constexpr int kTileBlocksPerSm = LIO_TILE_BLOCKS_PER_SM;  // resident blocks of k_knn_tile per SM (register budget 65536 / (128 * this))
 
 // DEV kernels belong to the device-resident IEKF loop (lio_iekf.cuh): the state comes from ctl->x instead of the launch
 // parameters.  Returns the state the block should use (block-wide; contains a barrier when DEV).
@@ -283,7 +287,7 @@ __device__ __forceinline__ const StateArg& block_state(const StateArg& st_param,
 // a task reads its 32 queries with one coalesced load; results are scattered back to the queries' own rows through `order`.
 // q = this search's counter set (zeroed by the previous search's k_knn_left).
 template <bool XFORM, bool DEV>
-__global__ void __launch_bounds__(kTileWarps * 32, 8) k_knn_tile(MapView m, const float4* __restrict__ sorted, const uint32_t* __restrict__ order,
+__global__ void __launch_bounds__(kTileWarps * 32, kTileBlocksPerSm) k_knn_tile(MapView m, const float4* __restrict__ sorted, const uint32_t* __restrict__ order,
                                                                int n, StateArg st_param, int k, float max_d2, float4* __restrict__ nn,
                                                                float* __restrict__ nn_d2, int* __restrict__ nn_cnt, TileQueue* __restrict__ q,
                                                                unsigned long long* __restrict__ queue, uint32_t qcap,
@@ -1240,7 +1244,7 @@ static int tile_order_graph(lio_ctx* c, int n, const double* state_host) {
 static int tile_grid(const lio_ctx* c, int n) {
   const int tiles = (n + 31) / 32;
   const int blocks = (tiles + kTileWarps - 1) / kTileWarps;
-  return std::max(1, std::min(blocks + blocks / 4 + 1, c->n_sms * 8));
+  return std::max(1, std::min(blocks + blocks / 4 + 1, c->n_sms * kTileBlocksPerSm));
 }
 
 // tasks (tiles + pushed sub-tiles) of the last search; its counter set stays intact until the next search has run
