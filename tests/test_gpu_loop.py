@@ -327,3 +327,22 @@ def test_pool_equals_single_context(loop_mod, closers, drive):
         for a, b in zip(got, ref):
             same_result(a, b)
         pool.close()
+
+
+@pytest.mark.parametrize("knob", [("LOOP_TREE", "balanced"), ("LOOP_GRID", "1"), ("LOOP_SAMPLE_FIRST", "0"), ("LOOP_TREE_ORDER", "morton")])
+def test_search_knobs_change_nothing(loop_mod, closers, drive, monkeypatch, knob):
+    """The A/B switches of the correspondence search (index-balanced tree, grid probe for seeded searches, cold first
+    iteration, Morton order) only change how the exact nearest neighbour is found: every result is bit-identical."""
+    g, _ = closers
+    clouds, est, _, stamps = drive
+    K = len(clouds)
+    pairs = [(K - 2 - i, 1 + (i % 3)) for i in range(5)]
+    ref = g.verify_batch(pairs)
+    monkeypatch.setenv(*knob)
+    h = loop_mod.LoopClosure(num_submap_keyframes=g.num_submap_keyframes)
+    for c, e, s in zip(clouds, est, stamps):
+        h.add_keyframe(c, e, s)
+    got = h.verify_batch(pairs)
+    for a, b in zip(got, ref):
+        same_result(a, b)
+    h.close()
