@@ -487,6 +487,7 @@ def compact_configs(args):
                                        "queries_per_s_1M_patch": big["patch"]["queries_per_s"], "fraction_of_gather_probe_1M_patch": big["patch"]["fraction_of_gather_probe_16B"],
                                        "queries_per_s_1M_spread_l2_flushed": big["spread"]["queries_per_s_l2_flushed"],
                                        "fraction_of_gather_probe_1M_spread": big["spread"]["fraction_of_gather_probe_16B"],
+                                       "dram_traffic_1M_spread": big["spread"].get("dram_traffic"),
                                        "gather_probe_GBps_16B": r["gather_probe"]["GBps_16B_requests"]}
     except Exception as e:
         out["configs[4] knn_sweep"] = {"error": str(e)[:200]}

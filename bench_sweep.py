@@ -8,6 +8,7 @@ regime of the search; exactness at full size is checked on a sam
 """
 import importlib
 import json
+import os
 import time
 
 import numpy as np
@@ -125,6 +126,17 @@ def run(args, spacings=(1.0, 0.5, 0.25, 0.125)):
                 rb = run_case(g, m, make_queries(m, n_big, mode=mode), reps, flush, torch)
                 rb.update({"filter_size_map": spacing, "query_set": mode,
                            "fraction_of_gather_probe_16B": rb["algorithmic_GBps_l2_flushed" if mode == "spread" else "algorithmic_GBps"] / probe[0]})
+                if mode == "spread" and n_big == 1_000_000 and n_map == 20_000_000:
+                    # DRAM bytes of this launch from the committed ncu --set full capture (a profiler number, never measured in a
+                    # bench run) over the search time measured live, against the 32-byte-sector rate of the random-gather probe
+                    try:
+                        tr = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")))["iekf_knn_20M_spread"]
+                        gbps = tr["bytes_per_launch"] / (rb["search_ms_l2_flushed"] * 1e-3) / 1e9
+                        rb["dram_traffic"] = {"bytes_per_launch": tr["bytes_per_launch"], "bytes_per_query": tr["bytes_per_launch"] / n_big,
+                                              "source": tr["source"], "GBps_over_live_search_time": gbps,
+                                              "fraction_of_gather_probe_32B_sectors": gbps / probe[1]}
+                    except (OSError, KeyError, ValueError):
+                        rb["dram_traffic"] = None
                 big.append(rb)
         g.close()
         del m

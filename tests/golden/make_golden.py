@@ -61,6 +61,50 @@ def loop_small():
     print("loop_small: src", src.shape, "dst", dst.shape, "iters", res["iterations"], "score", res["score"], "state", res["state"])
 
 
+def map_small_inputs():
+    """Ground patch + three scans: on the patch, in front of it (the far-neighbour branch of map_incremental decides), and
+    shifted; one box delete between the second and the third."""
+    g = np.arange(-6, 6, 0.5, dtype=np.float32) + 0.13
+    gx, gy = np.meshgrid(g, g)
+    m = np.stack([gx.ravel(), gy.ravel(), np.full(gx.size, 0.07, np.float32)], 1)
+    rng = np.random.default_rng(synth.SEED + 41)
+    scans = []
+    for k in range(3):
+        near = np.stack([rng.uniform(-5, 5, 250), rng.uniform(-5, 5, 250), rng.normal(0.07, 0.02, 250)], 1)
+        front = [np.array([8.0 + 2.0 * j + k, 1.1 * j - k, 0.3 * j]) + rng.uniform(0, 0.6, (10, 3)) for j in range(4)]
+        far = np.array([[50.0 + k, -44.0, 3.0]])
+        scans.append(np.ascontiguousarray(np.concatenate([near] + front + [far]).astype(np.float32)))
+    states = np.stack([synth.make_state(synth.rot_from_rpy(0, 0, 0.02 * k), np.array([0.3 * k, 0.1 * k, 0.0])) for k in range(3)])
+    boxes = np.array([[-7, -7, -1, -2, 7, 1], [9, -3, -1, 12, 3, 3]], np.float32)  # part of the patch, one front cluster
+    return m, scans, states, boxes
+
+
+def map_small_replay(ctx, m, scans, states, boxes):
+    """The same calls on any implementation of the map interface (oracle or the C-ABI view)."""
+    ctx.map_build(m)
+    counts, deleted = [], -1
+    for k, (scan, st) in enumerate(zip(scans, states)):
+        ctx.scan_upload(scan)
+        ctx.h_share(st, True)
+        counts.append(ctx.map_incremental(st, True))
+        if k == 1:
+            deleted = int(ctx.map_delete_boxes(boxes))
+    xyz, ids = ctx.map_export()
+    order = np.argsort(ids, kind="stable")
+    return np.array(counts, np.int32), deleted, xyz[order], ids[order]
+
+
+def map_small():
+    m, scans, states, boxes = map_small_inputs()
+    o = orc.OracleLio(0.5, nthreads=1)
+    counts, deleted, xyz, ids = map_small_replay(o, m, scans, states, boxes)
+    assert (counts[:, 1] > 0).all() and deleted > 0  # the far-neighbour branch and the delete were exercised
+    np.savez_compressed(os.path.join(HERE, "map_small.npz"), map=m, scan0=scans[0], scan1=scans[1], scan2=scans[2], states=states,
+                        boxes=boxes, counts=counts, deleted=deleted, xyz=xyz, ids=ids)
+    print("map_small: map", m.shape, "counts", counts.tolist(), "deleted", deleted, "final", xyz.shape)
+
+
 if __name__ == "__main__":
     lio_small()
     loop_small()
+    map_small()

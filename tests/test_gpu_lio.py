@@ -524,6 +524,16 @@ def test_map_incremental_far_neighbour_parity(pkg, orc, synth):
     os.environ.pop("LIO_MAP_GRAPH", None)
 
 
+def test_golden_map_small_gpu(pkg):
+    """The committed map fixture (three scans through map_incremental incl. the far-neighbour branch, one box delete)
+    replayed through the C-ABI: list sizes, deleted count and the final live map (ids and coordinates) bit-identical."""
+    from test_oracle_lio import _replay_map_small
+
+    g = pkg.LioContext(0.5, max_points=1 << 16, max_scan=4096)
+    _replay_map_small(g)
+    g.close()
+
+
 def _predict(state, dR, dt):
     """state (+) body-frame motion (dR, dt): pos += rot*dt, rot = rot*dR  (state layout of include/lio_b200.h)."""
     s = state.copy()
