@@ -106,6 +106,7 @@ LIO_SYMBOLS = {
     "lio_tile_profile": (C.c_int, [C.c_void_p, _u32p, C.c_int, _i32p]),
     "lio_gather_probe": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "lio_launch_count": (C.c_int64, [C.c_void_p]),
+    "lio_hth_reduce_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 
@@ -361,6 +362,18 @@ class LioContext:
 
     def launch_count(self):
         return int(self.lib.lio_launch_count(self.h))
+
+
+STATIC_REDUCE_MAX_ROWS = 1 << 20  # LIO_STATIC_REDUCE_MAX_ROWS
+
+
+def hth_reduce_static(rows_dev, z_dev, n, hth_dev, htz_dev, stream=None):
+    """lio_hth_reduce_static: rows^T rows / rows^T z from DEVICE addresses (ints), with no allocation on the way; the
+    per-block sums live in the library's static device array (shared by every call on the GPU).  Asynchronous on `stream`."""
+    lib = load_library()
+    rc = lib.lio_hth_reduce_static(rows_dev, z_dev, int(n), hth_dev, htz_dev, stream)
+    if rc != LIO_OK:
+        raise LioError(f"lio_hth_reduce_static failed ({rc}): {lib.lio_last_error().decode()}")
 
 
 def imu_predict(state, P, dt, acc, gyro, Q):

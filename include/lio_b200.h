@@ -177,6 +177,23 @@ int lio_gather_probe(lio_ctx* ctx, uint64_t table_bytes, int reps, double* gbps_
 /* number of kernels this context has launched since creation */
 int64_t lio_launch_count(lio_ctx* ctx);
 
+/* ---- allocation-free entry point -------------------------------------------------------------------- */
+/* No counterpart in the reference; added for callers that may not call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * The FP64 reduction that ends h_share_model, on its own: HTH[144] (row-major) = rows^T rows and HTz[12] = rows^T z
+ * for rows[n*12] / z[n] laid out as lio_h_share_rows returns them (rows of unselected points are zero).  ALL FOUR
+ * pointers are DEVICE pointers supplied by the caller, on the current device; `stream` is a cudaStream_t (NULL = the
+ * default stream) and the outputs are ready when the stream reaches this point.  The call makes no cudaMalloc /
+ * cudaFree and uses no allocating library routine: its per-block partial sums live in a static __device__ array of
+ * 768.25 KiB that every GPU loading the library holds until exit.  n > LIO_STATIC_REDUCE_MAX_ROWS (or n < 0, or a
+ * null pointer) -> LIO_E_ARG with the limit in lio_last_error(); split the rows and add the results instead.
+ * Every call on a device shares that array (it keeps the last call's contents; the call clears what must start at
+ * zero), so calls that overlap on one GPU - two streams, two host threads - race: serialise them.
+ * Sums are taken in a fixed order (rows in order within 1024-row blocks, blocks in order): bit-reproducible, and equal
+ * to lio_h_share's HTH / HTz up to FP64 summation order (tests: 1e-11 relative). */
+#define LIO_STATIC_REDUCE_MAX_ROWS (1 << 20)
+int lio_hth_reduce_static(const double* rows_dev, const double* z_dev, int n, double* HTH_dev, double* HTz_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
