@@ -40,6 +40,11 @@ __device__ __constant__ int c_tile_block = 0;
 // (27 cells staged per pass); default 0: its queries go to the per-query kernel (60 vs 62 us per search: the dense corners
 // that overflow are the slowest tasks of the launch, and serving them in the same warp lengthens its tail)
 __device__ __constant__ int c_tile_halve = 0;
+// LIO_TILE_SPLIT=n (0..8, default 8): a staging pass with at most n lanes still pending (offered sub-tile tasks, second passes
+// with a grown box) scans the staged points with FOUR lanes per query - lane 4g+p takes every 4th candidate for the g-th
+// pending lane - and merges the four top-6 lists by two exchange rounds, instead of leaving 24+ lanes idle for the whole scan.
+// Keys are unique (they carry the staged index), so the merged list is the list one lane would have built: same result.
+__device__ __constant__ int c_tile_split = 8;
 
 struct __align__(16) TileSmem {
   float4 pts[kTileCap];
@@ -282,30 +287,53 @@ __device__ __forceinline__ unsigned tile_search_sub(const MapView& m, TileSmem& 
     if (n_st < 0) return sub;  // too many cells / candidates
     bool done = false;
     int need = 0;
+    Top6T F;
+    F.clear();
+    const int act = __popc(sub);
+    if (act <= c_tile_split) {  // warp-uniform: four lanes per pending query
+      const int grp = lane >> 2, part = lane & 3;
+      const bool gact = grp < act;
+      unsigned rest = sub;
+      for (int i = 0; i < grp && i < 7; ++i) rest &= rest - 1u;
+      const int src = gact ? (__ffs(rest) - 1) : lane;  // the grp-th pending lane
+      const float sx = __shfl_sync(0xFFFFFFFFu, qx, src), sy = __shfl_sync(0xFFFFFFFFu, qy, src), sz = __shfl_sync(0xFFFFFFFFu, qz, src);
+      if (gact) {
+        for (int j = part; j < n_st; j += 4) {
+          const float4 c0 = sm.pts[j];
+          F.insert((__float_as_uint(sqdist3(sx, sy, sz, c0.x, c0.y, c0.z)) & 0xFFFFFF00u) | (uint32_t)j);
+        }
+      }
+#pragma unroll
+      for (int mm = 1; mm <= 2; mm <<= 1) {
+        const uint32_t o0 = __shfl_xor_sync(0xFFFFFFFFu, F.k0, mm), o1 = __shfl_xor_sync(0xFFFFFFFFu, F.k1, mm);
+        const uint32_t o2 = __shfl_xor_sync(0xFFFFFFFFu, F.k2, mm), o3 = __shfl_xor_sync(0xFFFFFFFFu, F.k3, mm);
+        const uint32_t o4 = __shfl_xor_sync(0xFFFFFFFFu, F.k4, mm), o5 = __shfl_xor_sync(0xFFFFFFFFu, F.k5, mm);
+        F.insert(o0), F.insert(o1), F.insert(o2), F.insert(o3), F.insert(o4), F.insert(o5);
+      }
+      const int from = (__popc(sub & ((1u << lane) - 1u)) << 2) & 31;  // a pending lane reads the list of its group
+      F.k0 = __shfl_sync(0xFFFFFFFFu, F.k0, from), F.k1 = __shfl_sync(0xFFFFFFFFu, F.k1, from), F.k2 = __shfl_sync(0xFFFFFFFFu, F.k2, from);
+      F.k3 = __shfl_sync(0xFFFFFFFFu, F.k3, from), F.k4 = __shfl_sync(0xFFFFFFFFu, F.k4, from), F.k5 = __shfl_sync(0xFFFFFFFFu, F.k5, from);
+    } else if (mine) {
+      int j = 0;
+      for (; j + 4 <= n_st; j += 4) {
+        const float4 c0 = sm.pts[j], c1 = sm.pts[j + 1], c2 = sm.pts[j + 2], c3 = sm.pts[j + 3];
+        const uint32_t d0 = __float_as_uint(sqdist3(qx, qy, qz, c0.x, c0.y, c0.z)), d1 = __float_as_uint(sqdist3(qx, qy, qz, c1.x, c1.y, c1.z));
+        const uint32_t d2 = __float_as_uint(sqdist3(qx, qy, qz, c2.x, c2.y, c2.z)), d3 = __float_as_uint(sqdist3(qx, qy, qz, c3.x, c3.y, c3.z));
+        F.insert((d0 & 0xFFFFFF00u) | (uint32_t)j);
+        F.insert((d1 & 0xFFFFFF00u) | (uint32_t)(j + 1));
+        F.insert((d2 & 0xFFFFFF00u) | (uint32_t)(j + 2));
+        F.insert((d3 & 0xFFFFFF00u) | (uint32_t)(j + 3));
+      }
+      for (; j < n_st; ++j) {
+        const float4 c0 = sm.pts[j];
+        F.insert((__float_as_uint(sqdist3(qx, qy, qz, c0.x, c0.y, c0.z)) & 0xFFFFFF00u) | (uint32_t)j);
+      }
+    }
     if (mine) {
       const uint32_t max_bits = __float_as_uint(max_d2);
       uint32_t r0, r1, r2, r3, r4;  // staged indices of the answer, ascending (d2, id)
-      int cnt;
-      {
-        Top6T F;
-        F.clear();
-        int j = 0;
-        for (; j + 4 <= n_st; j += 4) {
-          const float4 c0 = sm.pts[j], c1 = sm.pts[j + 1], c2 = sm.pts[j + 2], c3 = sm.pts[j + 3];
-          const uint32_t d0 = __float_as_uint(sqdist3(qx, qy, qz, c0.x, c0.y, c0.z)), d1 = __float_as_uint(sqdist3(qx, qy, qz, c1.x, c1.y, c1.z));
-          const uint32_t d2 = __float_as_uint(sqdist3(qx, qy, qz, c2.x, c2.y, c2.z)), d3 = __float_as_uint(sqdist3(qx, qy, qz, c3.x, c3.y, c3.z));
-          F.insert((d0 & 0xFFFFFF00u) | (uint32_t)j);
-          F.insert((d1 & 0xFFFFFF00u) | (uint32_t)(j + 1));
-          F.insert((d2 & 0xFFFFFF00u) | (uint32_t)(j + 2));
-          F.insert((d3 & 0xFFFFFF00u) | (uint32_t)(j + 3));
-        }
-        for (; j < n_st; ++j) {
-          const float4 c0 = sm.pts[j];
-          F.insert((__float_as_uint(sqdist3(qx, qy, qz, c0.x, c0.y, c0.z)) & 0xFFFFFF00u) | (uint32_t)j);
-        }
-        cnt = F.resolve(max_bits);
-        r0 = F.k0 & 0xFFu, r1 = F.k1 & 0xFFu, r2 = F.k2 & 0xFFu, r3 = F.k3 & 0xFFu, r4 = F.k4 & 0xFFu;
-      }
+      int cnt = F.resolve(max_bits);
+      r0 = F.k0 & 0xFFu, r1 = F.k1 & 0xFFu, r2 = F.k2 & 0xFFu, r3 = F.k3 & 0xFFu, r4 = F.k4 & 0xFFu;
       if (cnt < 0) {  // near-tie at the truncated precision (rare): exact list
         Top32 L;
         L.clear();

@@ -1049,6 +1049,9 @@ int scan_alloc(lio_ctx* c) {
       e = getenv("LIO_TILE_HALVE");
       const int halve = (e && e[0] == '1') ? 1 : 0;
       LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_halve, &halve, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
+      e = getenv("LIO_TILE_SPLIT");
+      const int split = e ? std::max(0, std::min(8, atoi(e))) : 8;
+      LIO_CUDA(cudaMemcpyToSymbolAsync(c_tile_split, &split, sizeof(int), 0, cudaMemcpyHostToDevice, c->stream));
       LIO_CUDA(cudaStreamSynchronize(c->stream));
     }
     e = getenv("LIO_TILE_PROF");  // per-tile cycle / pass counters of the last scan search (lio_tile_profile)
