@@ -39,6 +39,11 @@ for j in range(2):
         print(f"  timeline: last start {s_ns.max()} ns, last end {e_ns.max()} ns; start p50 {np.percentile(s_ns, 50):.0f} p90 {np.percentile(s_ns, 90):.0f} "
               f"p99 {np.percentile(s_ns, 99):.0f}; tile duration ns mean {(e_ns - s_ns).mean():.0f} p99 {np.percentile(e_ns - s_ns, 99):.0f} max {(e_ns - s_ns).max()}")
         print(f"  stage share of tile cycles {stc.sum() / cyc.sum():.3f}; SMs used {len(np.unique(smid))}; tiles per SM min {np.bincount(smid).min()} max {np.bincount(smid).max()}")
+        for name, mk in (("tiles", is_pushed == 0), ("pushed", is_pushed == 1)):
+            if mk.any():
+                print(f"  {name}: {int(mk.sum())} tasks, share of all task cycles {cyc[mk].sum() / cyc.sum():.3f}, cycles mean {cyc[mk].mean():.0f}, stage share {stc[mk].sum() / cyc[mk].sum():.3f}, "
+                      f"passes/task {passes[mk].mean():.2f}, cells/pass {cells[mk].sum() / max(1, passes[mk].sum()):.1f}, staged/pass {staged[mk].sum() / max(1, passes[mk].sum()):.1f}, "
+                      f"served/task {served[mk].mean():.1f}")
         end_sm = np.array([e_ns[smid == k].max() for k in np.unique(smid)])
         print(f"  per-SM last end ns: min {end_sm.min()} p50 {np.percentile(end_sm, 50):.0f} p90 {np.percentile(end_sm, 90):.0f} max {end_sm.max()}")
         alive = [(int(t), int(((s_ns <= t) & (e_ns > t)).sum())) for t in range(0, int(e_ns.max()) + 1, 4000)]
